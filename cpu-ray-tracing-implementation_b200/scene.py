@@ -1,0 +1,238 @@
+"""Flattened scene container: the host-side mirror of b200rt_scene_desc (include/b200rt.h).
+
+A Scene owns numpy arrays laid out exactly as the C ABI expects; `desc()` hands out a
+b200rt_scene_desc pointing into them.  Scenes come from three places:
+  * the reference-side adaptor (include/b200rt_adaptor.hpp) walking live reference objects —
+    `Scene.from_desc_pointer` copies such a description out of foreign memory;
+  * committed fixtures under tests/golden/*.npz (`Scene.load`);
+  * generators in this module for assets that are missing from the reference checkout
+    (Sponza stand-in mesh).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as abi
+
+_ARRAYS = [
+    # name, dtype, trailing shape
+    ("nodes", abi.node_dtype, ()),
+    ("list_children", np.dtype("<u4"), ()),
+    ("spheres", np.dtype("<f8"), (abi.SPHERE_STRIDE,)),
+    ("sphere_mat", np.dtype("<i4"), ()),
+    ("quads", np.dtype("<f8"), (abi.QUAD_STRIDE,)),
+    ("quad_mat", np.dtype("<i4"), ()),
+    ("tris", np.dtype("<f8"), (abi.TRI_STRIDE,)),
+    ("tri_mat", np.dtype("<i4"), ()),
+    ("volumes", abi.volume_dtype, ()),
+    ("materials", abi.material_dtype, ()),
+    ("textures", abi.texture_dtype, ()),
+    ("images", abi.image_dtype, ()),
+    ("image_bytes", np.dtype("u1"), ()),
+    ("perlin_vec", np.dtype("<f8"), (256, 3)),
+    ("perlin_perm", np.dtype("<i4"), (256,)),
+    ("value_noise", abi.value_noise_dtype, ()),
+    ("value_lattice", np.dtype("<f4"), ()),
+]
+_SCALARS = ["root", "n_primitives", "light_kind", "light_index", "background_tex"]
+
+
+def _view(ptr, count, dtype, shape):
+    """Copy `count` records of `dtype`+`shape` from raw address `ptr`."""
+    n_items = int(count)
+    full = (n_items,) + tuple(shape)
+    if n_items == 0 or not ptr:
+        return np.zeros(full, dtype=dtype)
+    nbytes = int(np.prod(full)) * dtype.itemsize
+    buf = (C.c_char * nbytes).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype).reshape(full).copy()
+
+
+class Scene:
+    def __init__(self):
+        for name, dt, shape in _ARRAYS:
+            setattr(self, name, np.zeros((0,) + shape, dtype=dt))
+        self.root = 0
+        self.n_primitives = 0
+        self.light_kind = abi.LIGHT_NONE
+        self.light_index = -1
+        self.background_tex = -1
+        self.name = ""
+
+    # ---- construction -------------------------------------------------------------------------
+    @classmethod
+    def from_desc_pointer(cls, ptr):
+        """Deep-copy a b200rt_scene_desc that lives in foreign (adaptor-owned) memory."""
+        d = C.cast(ptr, C.POINTER(abi.SceneDesc)).contents
+        if d.abi_version != abi.ABI_VERSION:
+            raise ValueError(f"scene description has ABI version {d.abi_version}, expected {abi.ABI_VERSION}")
+        s = cls()
+        counts = {
+            "nodes": d.n_nodes,
+            "list_children": d.n_list_children,
+            "spheres": d.n_spheres,
+            "sphere_mat": d.n_spheres,
+            "quads": d.n_quads,
+            "quad_mat": d.n_quads,
+            "tris": d.n_tris,
+            "tri_mat": d.n_tris,
+            "volumes": d.n_volumes,
+            "materials": d.n_materials,
+            "textures": d.n_textures,
+            "images": d.n_images,
+            "image_bytes": d.image_bytes_size,
+            "perlin_vec": d.n_perlin,
+            "perlin_perm": d.n_perlin,
+            "value_noise": d.n_value_noise,
+            "value_lattice": d.value_lattice_size,
+        }
+        for name, dt, shape in _ARRAYS:
+            setattr(s, name, _view(getattr(d, name), counts[name], dt, shape))
+        for k in _SCALARS:
+            setattr(s, k, int(getattr(d, k)))
+        return s
+
+    def save(self, path, **extra):
+        payload = {name: getattr(self, name) for name, _, _ in _ARRAYS}
+        payload["scalars"] = np.array([getattr(self, k) for k in _SCALARS], dtype=np.int64)
+        payload.update(extra)
+        np.savez_compressed(path, **payload)
+
+    @classmethod
+    def load(cls, path_or_npz):
+        z = np.load(path_or_npz) if not hasattr(path_or_npz, "files") else path_or_npz
+        s = cls()
+        for name, dt, shape in _ARRAYS:
+            arr = z[name]
+            setattr(s, name, np.ascontiguousarray(arr.astype(dt, copy=False)).reshape((-1,) + shape))
+        for k, v in zip(_SCALARS, z["scalars"].tolist()):
+            setattr(s, k, int(v))
+        return s
+
+    # ---- C ABI view -----------------------------------------------------------------------------
+    def desc(self):
+        """-> (b200rt_scene_desc, keepalive).  The description borrows this Scene's arrays."""
+        keep = []
+
+        def p(name):
+            a = np.ascontiguousarray(getattr(self, name))
+            keep.append(a)
+            return a.ctypes.data if a.size else None
+
+        d = abi.SceneDesc()
+        d.abi_version = abi.ABI_VERSION
+        d.root = self.root
+        d.n_nodes = len(self.nodes)
+        d.n_list_children = len(self.list_children)
+        d.nodes = p("nodes")
+        d.list_children = p("list_children")
+        d.n_spheres = len(self.sphere_mat)
+        d.n_quads = len(self.quad_mat)
+        d.n_tris = len(self.tri_mat)
+        d.n_volumes = len(self.volumes)
+        for name in ("spheres", "sphere_mat", "quads", "quad_mat", "tris", "tri_mat", "volumes", "materials", "textures",
+                     "images", "image_bytes", "perlin_vec", "perlin_perm", "value_noise", "value_lattice"):
+            setattr(d, name, p(name))
+        d.n_materials = len(self.materials)
+        d.n_textures = len(self.textures)
+        d.n_images = len(self.images)
+        d.n_perlin = len(self.perlin_perm)
+        d.n_value_noise = len(self.value_noise)
+        d.n_primitives = self.n_primitives
+        d.image_bytes_size = self.image_bytes.size
+        d.value_lattice_size = self.value_lattice.size
+        d.light_kind = self.light_kind
+        d.light_index = self.light_index
+        d.background_tex = self.background_tex
+        return d, keep
+
+    # ---- summaries ------------------------------------------------------------------------------
+    def counts(self):
+        return {
+            "nodes": len(self.nodes),
+            "spheres": len(self.sphere_mat),
+            "quads": len(self.quad_mat),
+            "tris": len(self.tri_mat),
+            "volumes": len(self.volumes),
+            "materials": len(self.materials),
+            "textures": len(self.textures),
+            "primitives": self.n_primitives,
+        }
+
+
+# --------------------------------------------------------------------------------------------------
+# Sponza stand-in (assets/Sponza/glTF/Sponza.bin is missing from the reference checkout,
+# /root/reference/.MISSING_LARGE_BLOBS).  A deterministic atrium with the real asset's triangle count
+# (262 267, from Sponza.gltf's accessors) and raw bounds x[-1920.9,1799.9] y[-126.4,1429.4]
+# z[-1182.8,1105.4]: floor, walls, two colonnade storeys of tessellated columns and
+# arches, banners.  Vertices are float32 like glTF positions.  Labelled "Sponza-standin" wherever used.
+SPONZA_TRIANGLES = 262_267
+SPONZA_BOUNDS = ((-1920.9, 1799.9), (-126.4, 1429.4), (-1182.8, 1105.4))
+
+
+def _grid_quad(o, u, v, nu, nv):
+    """Tessellate parallelogram o + s u + t v into nu x nv cells -> (2*nu*nv, 3, 3) float64."""
+    s = np.linspace(0.0, 1.0, nu + 1)
+    t = np.linspace(0.0, 1.0, nv + 1)
+    P = o[None, None, :] + s[:, None, None] * u[None, None, :] + t[None, :, None] * v[None, None, :]
+    a, b, c, d = P[:-1, :-1], P[1:, :-1], P[1:, 1:], P[:-1, 1:]
+    t1 = np.stack([a, b, c], axis=2).reshape(-1, 3, 3)
+    t2 = np.stack([a, c, d], axis=2).reshape(-1, 3, 3)
+    return np.concatenate([t1, t2], axis=0)
+
+
+def _column(cx, cz, y0, y1, r, seg, rings):
+    """Fluted column as a tessellated cylinder -> (2*seg*rings, 3, 3)."""
+    ang = np.linspace(0.0, 2.0 * np.pi, seg + 1)
+    ys = np.linspace(y0, y1, rings + 1)
+    rr = r * (1.0 + 0.06 * np.cos(8.0 * ang))
+    X = cx + rr[None, :] * np.cos(ang)[None, :] + 0.0 * ys[:, None]
+    Z = cz + rr[None, :] * np.sin(ang)[None, :] + 0.0 * ys[:, None]
+    Y = ys[:, None] + 0.0 * ang[None, :]
+    P = np.stack([X, Y, Z], axis=-1)
+    a, b, c, d = P[:-1, :-1], P[:-1, 1:], P[1:, 1:], P[1:, :-1]
+    t1 = np.stack([a, b, c], axis=2).reshape(-1, 3, 3)
+    t2 = np.stack([a, c, d], axis=2).reshape(-1, 3, 3)
+    return np.concatenate([t1, t2], axis=0)
+
+
+def sponza_standin_triangles(n_triangles=SPONZA_TRIANGLES, seed=7):
+    """-> (n_triangles, 9) float32, deterministic."""
+    (x0, x1), (y0, y1), (z0, z1) = SPONZA_BOUNDS
+    f = lambda *a: np.array(a, dtype=np.float64)
+    parts = []
+    # floor, ceiling band, four walls (coarse + fine tessellation like the real asset's mixed density)
+    parts.append(_grid_quad(f(x0, y0, z0), f(x1 - x0, 0, 0), f(0, 0, z1 - z0), 96, 64))
+    parts.append(_grid_quad(f(x0, y0, z0), f(x1 - x0, 0, 0), f(0, y1 - y0, 0), 80, 40))
+    parts.append(_grid_quad(f(x0, y0, z1), f(x1 - x0, 0, 0), f(0, y1 - y0, 0), 80, 40))
+    parts.append(_grid_quad(f(x0, y0, z0), f(0, 0, z1 - z0), f(0, y1 - y0, 0), 48, 40))
+    parts.append(_grid_quad(f(x1, y0, z0), f(0, 0, z1 - z0), f(0, y1 - y0, 0), 48, 40))
+    # gallery floors of the upper storey along both long sides
+    for zz0, zz1 in ((z0, z0 + 420.0), (z1 - 420.0, z1)):
+        parts.append(_grid_quad(f(x0, 560.0, zz0), f(x1 - x0, 0, 0), f(0, 0, zz1 - zz0), 96, 12))
+    # two storeys of columns on both sides
+    xs = np.linspace(x0 + 260.0, x1 - 260.0, 12)
+    for storey, (cy0, cy1, r) in enumerate(((y0, 540.0, 60.0), (580.0, 1080.0, 45.0))):
+        for zc in (z0 + 430.0, z1 - 430.0):
+            for xc in xs:
+                parts.append(_column(xc, zc, cy0, cy1, r, 48, 36))
+    # hanging banners (thin, slightly curved sheets)
+    for k, xc in enumerate(np.linspace(x0 + 500.0, x1 - 500.0, 6)):
+        o = f(xc, 300.0, -160.0 + 50.0 * (k % 3))
+        parts.append(_grid_quad(o, f(0, 0, 320.0), f(30.0, 620.0, 0), 40, 60))
+    tris = np.concatenate(parts, axis=0)
+    rng = np.random.RandomState(seed)
+    if len(tris) < n_triangles:
+        # fill up with small clutter triangles (ivy / vases / lion heads in the real asset) inside the bounds
+        need = n_triangles - len(tris)
+        centre = np.stack([rng.uniform(x0 + 50, x1 - 50, need), rng.uniform(y0 + 5, 1000.0, need), rng.uniform(z0 + 50, z1 - 50, need)], axis=1)
+        # cluster them near walls / columns so the atrium's centre stays open
+        centre[:, 2] = np.where(rng.rand(need) < 0.5, z0 + 60 + np.abs(rng.normal(0, 120, need)), z1 - 60 - np.abs(rng.normal(0, 120, need)))
+        off = rng.normal(0.0, 9.0, (need, 3, 3))
+        clutter = centre[:, None, :] + off
+        tris = np.concatenate([tris, clutter], axis=0)
+    tris = tris[:n_triangles]
+    lo = np.array([x0, y0, z0])
+    hi = np.array([x1, y1, z1])
+    tris = np.clip(tris, lo, hi)
+    return np.ascontiguousarray(tris.reshape(-1, 9).astype(np.float32))

@@ -1,0 +1,298 @@
+/*
+ * b200rt.h — C ABI of libb200rt.so, the B200 (sm_100a) path-tracing backend that
+ * replaces the per-pixel hot path of JTtNinjaCode/CPU-Ray-Tracing-Implementation:
+ *
+ *     camera::render's sample loop      (reference src/camera.h:135-176)
+ *     camera::ray_color  (recursive)    (reference src/camera.h:193-241)
+ *     camera::generate_ray / miss       (reference src/camera.h:244-284, 180-190)
+ *     and everything they call per sample (hittable::hit, material::scatter,
+ *     pdf::value/generate, texture::sample).
+ *
+ * The reference has no FFI: the path sits behind a C++ member call.  The C++
+ * adaptor in include/b200rt_adaptor.hpp walks the reference's polymorphic scene
+ * graph and fills the plain-old-data description below; this header is what
+ * that adaptor (and the ctypes mirror in cpu-ray-tracing-implementation_b200/)
+ * binds.  No C++ or torch types cross this boundary: plain pointers and sizes.
+ *
+ * Conventions
+ *   - every entry point returns 0 (B200RT_OK) or a negative b200rt_status;
+ *     b200rt_last_error() gives the message of the calling thread's last failure.
+ *   - the caller owns every host buffer; the library copies during the call.
+ *   - one context per GPU; contexts are independent; a context is not re-entrant.
+ *   - all geometry and radiance arithmetic is IEEE binary64, in the reference's
+ *     operation order and without fused multiply-add, so hit results are
+ *     bit-identical to the reference's x86-64 build.
+ */
+#ifndef B200RT_H
+#define B200RT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200RT_ABI_VERSION 1
+
+typedef enum b200rt_status {
+  B200RT_OK = 0,
+  B200RT_ERR_INVALID = -1,     /* bad argument / malformed scene description   */
+  B200RT_ERR_CUDA = -2,        /* a CUDA runtime call failed                    */
+  B200RT_ERR_UNSUPPORTED = -3, /* scene uses a construct the backend rejects    */
+  B200RT_ERR_STATE = -4        /* call order (render before upload, ...)        */
+} b200rt_status;
+
+/* ---------------------------------------------------------------- scene graph
+ * A node-for-node mirror of the reference's hittable graph, expanded to a tree
+ * (an object reachable along two paths is emitted twice, except the
+ * left_ == right_ case of one-object bvh_node, reference src/bvh_node.h:34-36,
+ * which keeps a == b so that the double visit is reproduced).
+ */
+typedef enum b200rt_node_kind {
+  B200RT_NODE_BVH = 0,       /* bvh_node       src/bvh_node.h:49-59   a=left b=right f=box{x0,x1,y0,y1,z0,z1} */
+  B200RT_NODE_LIST = 1,      /* hittable_list  src/hittable_list.h:20-31  a=first index in list_children, b=count */
+  B200RT_NODE_TRANSLATE = 2, /* translate      src/hittable.h:75-82   a=child f[0..2]=offset */
+  B200RT_NODE_ROTATE_X = 3,  /* rotate_x       src/hittable.h:125-149 a=child f[0]=sin f[1]=cos */
+  B200RT_NODE_ROTATE_Y = 4,  /* rotate_y       src/hittable.h:192-216 */
+  B200RT_NODE_ROTATE_Z = 5,  /* rotate_z       src/hittable.h:259-284 */
+  B200RT_NODE_SPHERE = 6,    /* sphere         src/sphere.h:40-74     a=index into spheres, c=primitive id */
+  B200RT_NODE_QUAD = 7,      /* quad           src/quad.h:30-52       a=index into quads,   c=primitive id */
+  B200RT_NODE_TRIANGLE = 8,  /* triangle       src/triangle.h:27-40   a=index into tris,    c=primitive id */
+  B200RT_NODE_VOLUME = 9     /* volumne        src/volumne.h:18-46    a=index into volumes, c=primitive id */
+} b200rt_node_kind;
+
+typedef struct b200rt_node {
+  int32_t kind; /* b200rt_node_kind */
+  int32_t a;
+  int32_t b;
+  int32_t c; /* leaves: primitive id (order of first visit in a left-to-right depth-first
+                walk from the root; what b200rt_trace returns); -1 inside a volume boundary */
+  double f[6];
+} b200rt_node;
+
+/* Geometry records, binary64, one row per object. */
+#define B200RT_SPHERE_STRIDE 12 /* center_[3] radius is_moving begin_center_[3] end_center_[3] pad  (src/sphere.h:98-106) */
+#define B200RT_QUAD_STRIDE 20   /* corner_[3] u_[3] v_[3] unorm_[3] w[3] D area pad[3]              (src/quad.h:81-87);
+                                   w = n/dot(n,n) with n = cross(u_,v_) and D = dot(unorm_,corner_) are
+                                   what quad::hit recomputes on every call (src/quad.h:32,39-40)          */
+#define B200RT_TRI_STRIDE 12    /* p0_[3] p1_[3] p2_[3] normal_[3]                                  (src/triangle.h:51-55) */
+
+typedef struct b200rt_volume {
+  int32_t boundary_node; /* root of the boundary sub-graph (leaves there carry c = -1) */
+  int32_t material;      /* the isotropic phase function, src/volumne.h:14 */
+  double density;
+} b200rt_volume;
+
+typedef enum b200rt_material_kind {
+  B200RT_MAT_LAMBERTIAN = 0,   /* src/material.h:57-76   */
+  B200RT_MAT_METAL = 1,        /* src/material.h:78-97   p0 = fuzz_ (float)  */
+  B200RT_MAT_DIELECTRIC = 2,   /* src/material.h:100-143 p0 = refract_ (float) */
+  B200RT_MAT_GLOSS = 3,        /* src/material.h:145-185 p0 = smoothness_ p1 = specular_prob_ (floats) */
+  B200RT_MAT_ISOTROPIC = 4,    /* src/material.h:187-204 */
+  B200RT_MAT_DIFFUSE_LIGHT = 5 /* src/material.h:206-219 */
+} b200rt_material_kind;
+
+typedef struct b200rt_material {
+  int32_t kind;
+  int32_t tex;
+  float p0;
+  float p1;
+} b200rt_material;
+
+typedef enum b200rt_texture_kind {
+  B200RT_TEX_SOLID = 0,   /* src/texture.h:12-37   c0 = colour */
+  B200RT_TEX_CHECKER = 1, /* src/texture.h:39-62   c0 = odd c1 = even scale */
+  B200RT_TEX_PICTURE = 2, /* src/texture.h:64-78   aux = image index */
+  B200RT_TEX_PERLIN = 3,  /* src/texture.h:80-93   aux = perlin table index, scale */
+  B200RT_TEX_VALUE = 4,   /* src/texture.h:95-103  aux = value-noise index */
+  B200RT_TEX_WORLEY = 5,  /* src/texture.h:105-111 */
+  B200RT_TEX_VORONOI = 6  /* src/texture.h:113-119 */
+} b200rt_texture_kind;
+
+typedef struct b200rt_texture {
+  int32_t kind;
+  int32_t aux;
+  double c0[3];
+  double c1[3];
+  double scale;
+} b200rt_texture;
+
+typedef struct b200rt_image { /* src/image.h:85-90; bytes are image::bdata, already 8-bit linear */
+  int32_t width;
+  int32_t height;
+  int32_t bytes_per_pixel; /* 3 (stb) or 4 (EXR) */
+  int32_t has_data;        /* 0: bdata == nullptr, lookups give magenta (src/image.h:75-76) */
+  uint64_t offset;         /* into image_bytes */
+} b200rt_image;
+
+typedef struct b200rt_value_noise { /* src/noise.h:95-137 */
+  int32_t resolution;
+  int32_t pad;
+  uint64_t offset; /* into value_lattice (floats), resolution^3 entries */
+} b200rt_value_noise;
+
+typedef enum b200rt_light_kind {
+  B200RT_LIGHT_NONE = 0,   /* render(out, world)           : material pdf only, src/camera.h:217-226 */
+  B200RT_LIGHT_QUAD = 1,   /* quad::pdf_value / random     : src/quad.h:66-78                          */
+  B200RT_LIGHT_SPHERE = 2, /* sphere::pdf_value / random   : src/sphere.h:76-81                        */
+  B200RT_LIGHT_DEFAULT = 3 /* hittable base: pdf 0, direction (1,0,0): src/hittable.h:39-41           */
+} b200rt_light_kind;
+
+typedef struct b200rt_scene_desc {
+  uint32_t abi_version; /* B200RT_ABI_VERSION */
+  uint32_t root;        /* node index of the world passed to camera::render */
+
+  uint32_t n_nodes;
+  uint32_t n_list_children;
+  const b200rt_node *nodes;
+  const uint32_t *list_children;
+
+  uint32_t n_spheres;
+  uint32_t n_quads;
+  uint32_t n_tris;
+  uint32_t n_volumes;
+  const double *spheres;      /* n_spheres x B200RT_SPHERE_STRIDE */
+  const int32_t *sphere_mat;  /* material index or -1 (nullptr material) */
+  const double *quads;        /* n_quads x B200RT_QUAD_STRIDE */
+  const int32_t *quad_mat;
+  const double *tris;         /* n_tris x B200RT_TRI_STRIDE */
+  const int32_t *tri_mat;
+  const b200rt_volume *volumes;
+
+  uint32_t n_materials;
+  uint32_t n_textures;
+  const b200rt_material *materials;
+  const b200rt_texture *textures;
+
+  uint32_t n_images;
+  uint32_t n_perlin;
+  uint32_t n_value_noise;
+  uint32_t n_primitives; /* number of distinct primitive ids (max c + 1) */
+  const b200rt_image *images;
+  const uint8_t *image_bytes;
+  uint64_t image_bytes_size;
+  const double *perlin_vec;   /* n_perlin x 256 x 3 : perlin::rand_offset (src/noise.h:72) */
+  const int32_t *perlin_perm; /* n_perlin x 256     : perlin::perm_x      (src/noise.h:73; the only table read, :36) */
+  const b200rt_value_noise *value_noise;
+  const float *value_lattice;
+  uint64_t value_lattice_size;
+
+  int32_t light_kind;   /* b200rt_light_kind: the `light` argument of camera::render (src/camera.h:135) */
+  int32_t light_index;  /* row in quads / spheres */
+  int32_t background_tex; /* camera::background_ (src/camera.h:329); -1 = nullptr */
+  int32_t reserved;
+} b200rt_scene_desc;
+
+/* ------------------------------------------------------------------- camera
+ * The public fields of the reference camera after initialize_* (src/camera.h:298-329).
+ */
+typedef enum b200rt_camera_mode {
+  B200RT_CAM_PERSPECTIVE = 0, /* src/camera.h:245-251 */
+  B200RT_CAM_ORTHOGRAPHIC = 1, /* src/camera.h:252-258 */
+  B200RT_CAM_FISHEYE = 2,     /* src/camera.h:259-275 */
+  B200RT_CAM_LENS = 3         /* src/camera.h:276-283 */
+} b200rt_camera_mode;
+
+typedef struct b200rt_camera {
+  int32_t mode;
+  int32_t image_width;
+  int32_t image_height;
+  int32_t samples_per_pixel;
+  int32_t max_depth;
+  int32_t reserved;
+  double viewport_width;
+  double viewport_height;
+  double focal_length;
+  double focus_dist;
+  double pos[3];
+  double dir[3];
+  double right[3];
+  double up[3];
+  double defocus_disk_u[3];
+  double defocus_disk_v[3];
+} b200rt_camera;
+
+/* ------------------------------------------------------------------ options */
+typedef enum b200rt_option {
+  B200RT_OPT_TRAVERSAL = 0,     /* 0 = compacted SAH BVH (default), 1 = node-for-node mirror of the reference graph */
+  B200RT_OPT_WAVE_PATHS = 1,    /* paths resident per wave (default 4 Mi)        */
+  B200RT_OPT_KILL_ZERO_WEIGHT = 2, /* 1 (default): drop paths whose throughput is exactly 0 in all channels */
+  B200RT_OPT_BVH_LEAF_SIZE = 3, /* max primitives per leaf of the compacted BVH  */
+  B200RT_OPT_SMEM_NODES = 4     /* top-of-tree nodes staged in shared memory      */
+} b200rt_option;
+
+#define B200RT_TRAVERSAL_FAST 0
+#define B200RT_TRAVERSAL_MIRROR 1
+
+typedef struct b200rt_stats {
+  uint64_t samples;       /* iterations of the k loop, src/camera.h:165-168             */
+  uint64_t rays;          /* world.hit calls issued from ray_color, src/camera.h:198    */
+  uint64_t nan_samples;   /* samples whose camera ray had a NaN direction (fisheye, outside the image circle) */
+  uint64_t kernel_launches;
+  double gpu_ms;          /* CUDA-event time of the kernels of this call                */
+  double extend_ms;       /* of which: traversal kernels                                 */
+  double h2d_bytes;
+  double d2h_bytes;
+} b200rt_stats;
+
+typedef struct b200rt_ctx b200rt_ctx;
+
+/* Create a context on CUDA device `device`. */
+int b200rt_create(int device, b200rt_ctx **out);
+int b200rt_destroy(b200rt_ctx *ctx);
+const char *b200rt_last_error(void);
+int b200rt_abi_version(void);
+
+int b200rt_set_option(b200rt_ctx *ctx, int option, double value);
+
+/* Replaces: scene hand-over at camera::render(out, world, light) (src/camera.h:135) plus the
+ * bvh_node constructor (src/bvh_node.h:18-47): copies the description, builds the compacted
+ * BVH on the host and uploads everything once. */
+int b200rt_upload_scene(b200rt_ctx *ctx, const b200rt_scene_desc *scene);
+
+/* Replaces: camera::initialize_* hand-over (src/camera.h:21,52,74,104). */
+int b200rt_set_camera(b200rt_ctx *ctx, const b200rt_camera *camera);
+
+/* Replaces: world.hit(r, interval(tmin,tmax), record) (src/camera.h:198 -> src/bvh_node.h:49-59)
+ * on a batch.  rays7 = n x {origin[3], direction[3], time}.  Host buffers.  Any output may be NULL.
+ *   prim  : primitive id of the returned record, -1 on miss
+ *   t     : record.t                          uv   : record.u, record.v (n x 2)
+ *   front : record.front_face                 p    : record.p (n x 3)     normal: record.normal (n x 3)
+ * `seed` keys the free-flight draw of volumes (src/volumne.h:36); ray i uses stream i. */
+int b200rt_trace(b200rt_ctx *ctx, const double *rays7, size_t n, double tmin, double tmax, uint64_t seed,
+                 int32_t *prim, double *t, double *uv, uint8_t *front, double *p, double *normal);
+
+/* Replaces: generate_ray(i, j, du, dv) (src/camera.h:244-284) for samples [spp_begin, spp_end) of every
+ * pixel; writes rays7 for pixel-major order  index = (sample - spp_begin) * W*H + (i*W + j).  Host buffer. */
+int b200rt_generate_rays(b200rt_ctx *ctx, uint64_t seed, int spp_begin, int spp_end, double *rays7);
+
+/* Replaces: the sample loop of camera::render (src/camera.h:158-172) for samples [spp_begin, spp_end):
+ * rgb_sum[(i*W+j)*3 + c] receives the SUM of ray_color over that sample range (divide by the total
+ * sample count after combining ranges).  Host buffer; the device->host copy is part of the call. */
+int b200rt_render(b200rt_ctx *ctx, uint64_t seed, int spp_begin, int spp_end, double *rgb_sum, b200rt_stats *stats);
+
+/* Same, accumulating (+=) into a DEVICE buffer of W*H*3 doubles on `cuda_stream` (a cudaStream_t, may be 0);
+ * asynchronous unless stats != NULL.  This is what the multi-GPU driver reduces with NCCL. */
+int b200rt_render_device(b200rt_ctx *ctx, uint64_t seed, int spp_begin, int spp_end, double *d_rgb_sum,
+                         void *cuda_stream, b200rt_stats *stats);
+
+/* Replaces: pixel_color /= spp and write_color (src/camera.h:169, src/color.h:16-36):
+ * rgb_linear = rgb_sum / total_spp (may alias); ppm_rgb (may be NULL) gets int(255.999 * pow(c, 1/2.2)), unclamped. */
+int b200rt_finalize(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, double *rgb_linear, int32_t *ppm_rgb);
+
+/* Introspection used by tests and the benchmark. */
+typedef struct b200rt_bvh_info {
+  uint32_t n_nodes;
+  uint32_t n_leaves;
+  uint32_t n_prims;
+  uint32_t max_depth;
+  double build_ms;
+  double sah_cost;
+} b200rt_bvh_info;
+int b200rt_bvh_info_get(b200rt_ctx *ctx, b200rt_bvh_info *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RT_H */
