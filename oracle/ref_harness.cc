@@ -94,9 +94,11 @@ void tls_seed(uint64_t a, uint64_t b) {
   t_rng_state = s;
 }
 } // namespace
+thread_local std::vector<int> *t_rand_log = nullptr; // when set, every value handed to the reference is recorded
 extern "C" int rand(void) {
-  if (g_rng_mode == 0) return libc_rand()();
-  return (int)(splitmix(t_rng_state) >> 33); // 31 bits, 0..RAND_MAX
+  int v = (g_rng_mode == 0) ? libc_rand()() : (int)(splitmix(t_rng_state) >> 33); // 31 bits, 0..RAND_MAX
+  if (t_rand_log) t_rand_log->push_back(v);
+  return v;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -632,6 +634,36 @@ int ref_generate_rays(int h, unsigned seed, int spp, double *rays7) {
         for (int c = 0; c < 3; c++) o[c] = r.origin().e[c], o[3 + c] = r.direction().e[c];
         o[6] = r.time();
       }
+  return 0;
+}
+
+// Same, also returning the std::rand values each generate_ray call consumed, in consumption order
+// (as random_double values, src/utility.h:20): draws[i*max_draws + k], counts[i].  Lets the restatement
+// be checked bit for bit on identical draws.
+int ref_generate_rays_logged(int h, unsigned seed, int spp, double *rays7, double *draws, int max_draws, int32_t *counts) {
+  scene *s = get(h);
+  if (!s) return -1;
+  camera &cam = s->cam;
+  g_rng_mode = 0;
+  srand(seed);
+  point3 du = cam.viewport_width_ * cam.right_ / cam.image_width_;
+  point3 dv = -cam.viewport_height_ * cam.up_ / cam.image_height_;
+  size_t npix = (size_t)cam.image_width_ * cam.image_height_;
+  std::vector<int> log;
+  t_rand_log = &log;
+  for (int k = 0; k < spp; k++)
+    for (int i = 0; i < cam.image_height_; i++)
+      for (int j = 0; j < cam.image_width_; j++) {
+        log.clear();
+        ray r = cam.generate_ray(i, j, du, dv);
+        size_t idx = k * npix + (size_t)i * cam.image_width_ + j;
+        double *o = rays7 + 7 * idx;
+        for (int c = 0; c < 3; c++) o[c] = r.origin().e[c], o[3 + c] = r.direction().e[c];
+        o[6] = r.time();
+        counts[idx] = (int32_t)log.size();
+        for (int q = 0; q < max_draws; q++) draws[idx * max_draws + q] = q < (int)log.size() ? log[q] / (RAND_MAX + 1.0) : 0.0;
+      }
+  t_rand_log = nullptr;
   return 0;
 }
 

@@ -153,3 +153,17 @@ class RefScene:
         img = np.zeros(self.npix * 3, np.float64)
         secs = lib().ref_render_stock(self.h, seed, spp, ppm_path.encode() if ppm_path else None, img.ctypes.data)
         return secs, img.reshape(self.camera.image_height, self.camera.image_width, 3)
+
+
+def _generate_rays_logged(self, seed, spp=1, max_draws=40):
+    n = spp * self.npix
+    rays = np.zeros((n, 7), np.float64)
+    draws = np.zeros((n, max_draws), np.float64)
+    counts = np.zeros(n, np.int32)
+    L = lib()
+    L.ref_generate_rays_logged.argtypes = [C.c_int, C.c_uint, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    assert L.ref_generate_rays_logged(self.h, seed, spp, rays.ctypes.data, draws.ctypes.data, max_draws, counts.ctypes.data) == 0
+    return rays, draws, counts
+
+
+RefScene.generate_rays_logged = _generate_rays_logged
