@@ -1,0 +1,615 @@
+// api.cu — the C ABI of libb200rt.so (include/b200rt.h): context, scene upload, and the host side of the
+// wavefront loop.  No CPU rendering path exists in this library: every entry point that produces rays,
+// hits or radiance launches the sm_100a kernels of shade_kernels.cuh / wavefront.cuh.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <mutex>
+
+#include "bvh_build.h"
+#include "shade_kernels.cuh"
+
+using namespace b200;
+
+namespace {
+
+thread_local std::string t_err;
+int fail(int code, const char *fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  t_err = buf;
+  return code;
+}
+#define CU(x)                                                                                                          \
+  do {                                                                                                                 \
+    cudaError_t e_ = (x);                                                                                              \
+    if (e_ != cudaSuccess) return fail(B200RT_ERR_CUDA, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+struct DevMem { // owns device allocations of a context
+  std::vector<void *> ptrs;
+  size_t bytes = 0;
+  ~DevMem() { release(); }
+  void release() {
+    for (void *p : ptrs) cudaFree(p);
+    ptrs.clear();
+    bytes = 0;
+  }
+  cudaError_t alloc(void **p, size_t n) {
+    if (n == 0) n = 16;
+    cudaError_t e = cudaMalloc(p, n);
+    if (e == cudaSuccess) ptrs.push_back(*p), bytes += n;
+    return e;
+  }
+};
+
+} // namespace
+
+struct b200rt_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // options
+  int traversal = B200RT_TRAVERSAL_FAST;
+  uint32_t wave_paths = 1u << 22;
+  int kill_zero = 1;
+  int bvh_leaf = 2;
+  // scene
+  bool have_scene = false, have_camera = false;
+  DevMem scene_mem;
+  DevScene S{};
+  b200rt_bvh_info bvh_info{};
+  double scene_h2d_bytes = 0;
+  int graph_depth = 0;
+  // camera
+  b200rt_camera cam{};
+  // wavefront pools
+  DevMem wave_mem;
+  uint32_t wave_capacity = 0;
+  bool wave_mirror = false;
+  PathBuf pool[2]{};
+  HitRef *hits = nullptr;
+  Rec *recs = nullptr;
+  Queues queues{};
+  WaveCtl *ctl = nullptr;
+  WaveCtl *h_ctl = nullptr; // pinned
+  double *accum = nullptr;  // W*H*3, used by b200rt_render
+  size_t accum_elems = 0;
+};
+
+namespace {
+
+template <class T> int upload(b200rt_ctx *c, const T *src, size_t count, const T **dst, const char *what) {
+  void *p = nullptr;
+  if (count && !src) return fail(B200RT_ERR_INVALID, "scene description: %s is NULL but its count is %zu", what, count);
+  CU(c->scene_mem.alloc(&p, count * sizeof(T)));
+  if (count) CU(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  c->scene_h2d_bytes += (double)(count * sizeof(T));
+  *dst = static_cast<const T *>(p);
+  return B200RT_OK;
+}
+#define UP(src, count, dst, what)                                                                                      \
+  do {                                                                                                                 \
+    int rc_ = upload(c, src, (size_t)(count), dst, what);                                                              \
+    if (rc_ != B200RT_OK) return rc_;                                                                                  \
+  } while (0)
+
+int validate(const b200rt_scene_desc *d) {
+  if (!d) return fail(B200RT_ERR_INVALID, "scene description is NULL");
+  if (d->abi_version != B200RT_ABI_VERSION) return fail(B200RT_ERR_INVALID, "scene description has ABI version %u, library has %d", d->abi_version, B200RT_ABI_VERSION);
+  if (d->n_nodes && d->root >= d->n_nodes) return fail(B200RT_ERR_INVALID, "root %u out of range (%u nodes)", d->root, d->n_nodes);
+  for (uint32_t i = 0; i < d->n_volumes; i++) {
+    if (d->volumes[i].material < 0 || (uint32_t)d->volumes[i].material >= d->n_materials) return fail(B200RT_ERR_INVALID, "volume %u: material out of range", i);
+    if (d->volumes[i].boundary_node < 0 || (uint32_t)d->volumes[i].boundary_node >= d->n_nodes) return fail(B200RT_ERR_INVALID, "volume %u: boundary node out of range", i);
+  }
+  for (uint32_t i = 0; i < d->n_materials; i++) {
+    const b200rt_material &m = d->materials[i];
+    if (m.kind < 0 || m.kind > B200RT_MAT_DIFFUSE_LIGHT) return fail(B200RT_ERR_UNSUPPORTED, "material %u: unknown kind %d", i, m.kind);
+    if (m.tex < 0 || (uint32_t)m.tex >= d->n_textures) return fail(B200RT_ERR_INVALID, "material %u: texture out of range", i);
+  }
+  for (uint32_t i = 0; i < d->n_textures; i++) {
+    const b200rt_texture &t = d->textures[i];
+    if (t.kind < 0 || t.kind > B200RT_TEX_VORONOI) return fail(B200RT_ERR_UNSUPPORTED, "texture %u: unknown kind %d", i, t.kind);
+    if (t.kind == B200RT_TEX_PICTURE && (t.aux < 0 || (uint32_t)t.aux >= d->n_images)) return fail(B200RT_ERR_INVALID, "texture %u: image out of range", i);
+    if (t.kind == B200RT_TEX_PERLIN && (t.aux < 0 || (uint32_t)t.aux >= d->n_perlin)) return fail(B200RT_ERR_INVALID, "texture %u: perlin table out of range", i);
+    if (t.kind == B200RT_TEX_VALUE && (t.aux < 0 || (uint32_t)t.aux >= d->n_value_noise)) return fail(B200RT_ERR_INVALID, "texture %u: value-noise table out of range", i);
+  }
+  for (uint32_t i = 0; i < d->n_images; i++) {
+    const b200rt_image &im = d->images[i];
+    if (im.has_data && (im.width <= 0 || im.height <= 0 || (im.bytes_per_pixel != 3 && im.bytes_per_pixel != 4) ||
+                        im.offset + (uint64_t)im.width * im.height * im.bytes_per_pixel > d->image_bytes_size))
+      return fail(B200RT_ERR_INVALID, "image %u: bad geometry or bytes out of range", i);
+  }
+  if (d->background_tex >= (int32_t)d->n_textures) return fail(B200RT_ERR_INVALID, "background texture out of range");
+  if (d->light_kind == B200RT_LIGHT_QUAD && (d->light_index < 0 || (uint32_t)d->light_index >= d->n_quads)) return fail(B200RT_ERR_INVALID, "light quad out of range");
+  if (d->light_kind == B200RT_LIGHT_SPHERE && (d->light_index < 0 || (uint32_t)d->light_index >= d->n_spheres)) return fail(B200RT_ERR_INVALID, "light sphere out of range");
+  if (d->light_kind < 0 || d->light_kind > B200RT_LIGHT_DEFAULT) return fail(B200RT_ERR_INVALID, "unknown light kind %d", d->light_kind);
+  return B200RT_OK;
+}
+
+} // namespace
+
+// ================================================================================================ C ABI
+extern "C" {
+
+const char *b200rt_last_error(void) { return t_err.c_str(); }
+int b200rt_abi_version(void) { return B200RT_ABI_VERSION; }
+
+// sizes of the ABI structures as compiled; the ctypes mirror checks itself against these
+size_t b200rt_abi_sizeof(int which) {
+  switch (which) {
+  case 0: return sizeof(b200rt_scene_desc);
+  case 1: return sizeof(b200rt_camera);
+  case 2: return sizeof(b200rt_stats);
+  case 3: return sizeof(b200rt_node);
+  case 4: return sizeof(b200rt_material);
+  case 5: return sizeof(b200rt_texture);
+  case 6: return sizeof(b200rt_image);
+  case 7: return sizeof(b200rt_volume);
+  case 8: return sizeof(b200rt_value_noise);
+  case 9: return sizeof(b200rt_bvh_info);
+  }
+  return 0;
+}
+
+int b200rt_create(int device, b200rt_ctx **out) {
+  if (!out) return fail(B200RT_ERR_INVALID, "b200rt_create: out is NULL");
+  *out = nullptr;
+  int n = 0;
+  CU(cudaGetDeviceCount(&n));
+  if (device < 0 || device >= n) return fail(B200RT_ERR_INVALID, "b200rt_create: device %d out of range (%d CUDA devices)", device, n);
+  CU(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) return fail(B200RT_ERR_UNSUPPORTED, "b200rt_create: device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor);
+  std::unique_ptr<b200rt_ctx> c(new b200rt_ctx);
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CU(cudaEventCreate(&c->ev0));
+  CU(cudaEventCreate(&c->ev1));
+  CU(cudaMallocHost(&c->h_ctl, sizeof(WaveCtl)));
+  *out = c.release();
+  return B200RT_OK;
+}
+
+int b200rt_destroy(b200rt_ctx *c) {
+  if (!c) return B200RT_OK;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  c->scene_mem.release();
+  c->wave_mem.release();
+  if (c->h_ctl) cudaFreeHost(c->h_ctl);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return B200RT_OK;
+}
+
+int b200rt_set_option(b200rt_ctx *c, int option, double value) {
+  if (!c) return fail(B200RT_ERR_INVALID, "context is NULL");
+  switch (option) {
+  case B200RT_OPT_TRAVERSAL:
+    if (value != B200RT_TRAVERSAL_FAST && value != B200RT_TRAVERSAL_MIRROR) return fail(B200RT_ERR_INVALID, "traversal must be 0 (compacted BVH) or 1 (mirror)");
+    c->traversal = (int)value;
+    return B200RT_OK;
+  case B200RT_OPT_WAVE_PATHS:
+    if (!(value >= 1024 && value <= 268435456.0)) return fail(B200RT_ERR_INVALID, "wave paths must be in [1024, 2^28]");
+    c->wave_paths = (uint32_t)value;
+    return B200RT_OK;
+  case B200RT_OPT_KILL_ZERO_WEIGHT: c->kill_zero = value != 0; return B200RT_OK;
+  case B200RT_OPT_BVH_LEAF_SIZE:
+    if (!(value >= 1 && value <= 8)) return fail(B200RT_ERR_INVALID, "leaf size must be in [1, 8]");
+    c->bvh_leaf = (int)value; // takes effect at the next b200rt_upload_scene
+    return B200RT_OK;
+  case B200RT_OPT_SMEM_NODES: return B200RT_OK; // reserved
+  }
+  return fail(B200RT_ERR_INVALID, "unknown option %d", option);
+}
+
+int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
+  if (!c) return fail(B200RT_ERR_INVALID, "context is NULL");
+  int rc = validate(d);
+  if (rc != B200RT_OK) return rc;
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize(c->stream));
+  c->have_scene = false;
+  c->scene_mem.release();
+  c->scene_h2d_bytes = 0;
+
+  // host: reference visiting order + transform chains + world boxes, then our own BVH
+  FlatScene fs;
+  BuiltBvh bvh;
+  std::vector<Entry> ordered;
+  try {
+    Flattener fl(*d);
+    fl.run();
+    fs = std::move(fl.out);
+    for (const Entry &e : fs.entries) {
+      int mat = -1;
+      switch (entry_kind(e)) {
+      case E_SPHERE:
+      case E_SPHERE_MOVING: mat = d->sphere_mat[e.row]; break;
+      case E_QUAD: mat = d->quad_mat[e.row]; break;
+      case E_TRI: mat = d->tri_mat[e.row]; break;
+      default: mat = 0; break;
+      }
+      if (mat < 0 || (uint32_t)mat >= d->n_materials)
+        return fail(B200RT_ERR_UNSUPPORTED, "primitive %d has no material (the reference would dereference a null pointer)", e.prim);
+    }
+    bvh = BvhBuilder(fs.boxes, c->bvh_leaf).run();
+    ordered.resize(fs.entries.size());
+    for (size_t k = 0; k < ordered.size(); k++) ordered[k] = fs.entries[bvh.perm[k]];
+  } catch (const std::exception &e) {
+    return fail(B200RT_ERR_INVALID, "scene description: %s", e.what());
+  }
+
+  DevScene S;
+  std::memset(&S, 0, sizeof S);
+  S.root = d->root;
+  UP(d->nodes, d->n_nodes, &S.nodes, "nodes");
+  UP(d->list_children, d->n_list_children, &S.list_children, "list_children");
+  UP(d->spheres, (size_t)d->n_spheres * B200RT_SPHERE_STRIDE, &S.spheres, "spheres");
+  UP(d->sphere_mat, d->n_spheres, &S.sphere_mat, "sphere_mat");
+  UP(d->quads, (size_t)d->n_quads * B200RT_QUAD_STRIDE, &S.quads, "quads");
+  UP(d->quad_mat, d->n_quads, &S.quad_mat, "quad_mat");
+  UP(d->tris, (size_t)d->n_tris * B200RT_TRI_STRIDE, &S.tris, "tris");
+  UP(d->tri_mat, d->n_tris, &S.tri_mat, "tri_mat");
+  UP(d->volumes, d->n_volumes, &S.volumes, "volumes");
+  UP(d->materials, d->n_materials, &S.materials, "materials");
+  UP(d->textures, d->n_textures, &S.textures, "textures");
+  UP(d->images, d->n_images, &S.images, "images");
+  UP(d->image_bytes, d->image_bytes_size, &S.image_bytes, "image_bytes");
+  UP(d->perlin_vec, (size_t)d->n_perlin * 768, &S.perlin_vec, "perlin_vec");
+  UP(d->perlin_perm, (size_t)d->n_perlin * 256, &S.perlin_perm, "perlin_perm");
+  UP(d->value_noise, d->n_value_noise, &S.value_noise, "value_noise");
+  UP(d->value_lattice, d->value_lattice_size, &S.value_lattice, "value_lattice");
+  S.light_kind = d->light_kind;
+  S.light_index = d->light_index;
+  S.background_tex = d->background_tex;
+  UP(bvh.nodes.data(), bvh.nodes.size(), &S.bvh, "bvh");
+  UP(ordered.data(), ordered.size(), &S.entries, "entries");
+  UP(fs.bentries.data(), fs.bentries.size(), &S.bentries, "bentries");
+  UP(fs.vol_inst.data(), fs.vol_inst.size(), &S.vol_inst, "vol_inst");
+  UP(fs.chain_ops.data(), fs.chain_ops.size(), &S.chain_ops, "chain_ops");
+  UP(fs.chains.data(), fs.chains.size(), &S.chains, "chains");
+  S.bvh_root = bvh.root;
+  S.n_bvh_nodes = (uint32_t)bvh.nodes.size();
+  S.n_entries = (uint32_t)ordered.size();
+  S.has_volumes = fs.has_volumes ? 1 : 0;
+  CU(cudaStreamSynchronize(c->stream)); // host vectors go out of scope
+  c->S = S;
+  c->bvh_info.n_nodes = (uint32_t)bvh.nodes.size();
+  c->bvh_info.n_leaves = bvh.n_leaves;
+  c->bvh_info.n_prims = (uint32_t)ordered.size();
+  c->bvh_info.max_depth = bvh.max_depth;
+  c->bvh_info.build_ms = bvh.build_ms;
+  c->bvh_info.sah_cost = bvh.sah_cost;
+  c->graph_depth = fs.graph_depth;
+  c->have_scene = true;
+  return B200RT_OK;
+}
+
+int b200rt_bvh_info_get(b200rt_ctx *c, b200rt_bvh_info *out) {
+  if (!c || !out) return fail(B200RT_ERR_INVALID, "NULL argument");
+  if (!c->have_scene) return fail(B200RT_ERR_STATE, "no scene uploaded");
+  *out = c->bvh_info;
+  return B200RT_OK;
+}
+
+int b200rt_set_camera(b200rt_ctx *c, const b200rt_camera *cam) {
+  if (!c || !cam) return fail(B200RT_ERR_INVALID, "NULL argument");
+  if (cam->mode < B200RT_CAM_PERSPECTIVE || cam->mode > B200RT_CAM_LENS) return fail(B200RT_ERR_INVALID, "unknown camera mode %d", cam->mode);
+  if (cam->image_width <= 0 || cam->image_height <= 0) return fail(B200RT_ERR_INVALID, "image size %dx%d", cam->image_width, cam->image_height);
+  if ((uint64_t)cam->image_width * cam->image_height >= 0xFFFFFFFFull) return fail(B200RT_ERR_INVALID, "image too large");
+  c->cam = *cam;
+  c->have_camera = true;
+  return B200RT_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+int grid_for(const b200rt_ctx *c, size_t n, int block, int per_sm) {
+  size_t g = (n + block - 1) / block;
+  const size_t cap = (size_t)c->sm_count * per_sm;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+// the mirror traversal recurses on the device: reserve a stack deep enough for this scene's graph
+int prepare_mirror(b200rt_ctx *c) {
+  const size_t want = 4096 + (size_t)c->graph_depth * 768;
+  size_t have = 0;
+  CU(cudaDeviceGetLimit(&have, cudaLimitStackSize));
+  if (have < want) CU(cudaDeviceSetLimit(cudaLimitStackSize, want));
+  return B200RT_OK;
+}
+
+struct ScratchFree {
+  std::vector<void *> p;
+  ~ScratchFree() {
+    for (void *q : p) cudaFree(q);
+  }
+};
+
+} // namespace
+
+extern "C" {
+
+int b200rt_trace(b200rt_ctx *c, const double *rays7, size_t n, double tmin, double tmax, uint64_t seed, int32_t *prim, double *t, double *uv,
+                 uint8_t *front, double *p, double *normal) {
+  if (!c) return fail(B200RT_ERR_INVALID, "context is NULL");
+  if (!c->have_scene) return fail(B200RT_ERR_STATE, "b200rt_trace before b200rt_upload_scene");
+  if (n == 0) return B200RT_OK;
+  if (!rays7) return fail(B200RT_ERR_INVALID, "rays7 is NULL");
+  CU(cudaSetDevice(c->device));
+  ScratchFree sf;
+  auto dalloc = [&](void **q, size_t bytes) {
+    cudaError_t e = cudaMalloc(q, bytes);
+    if (e == cudaSuccess) sf.p.push_back(*q);
+    return e;
+  };
+  double *d_rays = nullptr, *d_t = nullptr, *d_uv = nullptr, *d_p = nullptr, *d_n = nullptr;
+  int32_t *d_prim = nullptr;
+  uint8_t *d_front = nullptr;
+  CU(dalloc((void **)&d_rays, n * 7 * sizeof(double)));
+  CU(cudaMemcpyAsync(d_rays, rays7, n * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if (prim) CU(dalloc((void **)&d_prim, n * sizeof(int32_t)));
+  if (t) CU(dalloc((void **)&d_t, n * sizeof(double)));
+  if (uv) CU(dalloc((void **)&d_uv, n * 2 * sizeof(double)));
+  if (front) CU(dalloc((void **)&d_front, n));
+  if (p) CU(dalloc((void **)&d_p, n * 3 * sizeof(double)));
+  if (normal) CU(dalloc((void **)&d_n, n * 3 * sizeof(double)));
+  const int grid = grid_for(c, n, 128, 16);
+  if (c->traversal == B200RT_TRAVERSAL_MIRROR) {
+    int rc = prepare_mirror(c);
+    if (rc != B200RT_OK) return rc;
+    k_trace<true><<<grid, 128, 0, c->stream>>>(c->S, d_rays, n, tmin, tmax, seed, d_prim, d_t, d_uv, d_front, d_p, d_n);
+  } else {
+    k_trace<false><<<grid, 128, 0, c->stream>>>(c->S, d_rays, n, tmin, tmax, seed, d_prim, d_t, d_uv, d_front, d_p, d_n);
+  }
+  CU(cudaGetLastError());
+  if (prim) CU(cudaMemcpyAsync(prim, d_prim, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  if (t) CU(cudaMemcpyAsync(t, d_t, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (uv) CU(cudaMemcpyAsync(uv, d_uv, n * 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (front) CU(cudaMemcpyAsync(front, d_front, n, cudaMemcpyDeviceToHost, c->stream));
+  if (p) CU(cudaMemcpyAsync(p, d_p, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (normal) CU(cudaMemcpyAsync(normal, d_n, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200RT_OK;
+}
+
+int b200rt_texture_sample(b200rt_ctx *c, int tex, const double *uvp5, size_t n, double *rgb) {
+  if (!c) return fail(B200RT_ERR_INVALID, "context is NULL");
+  if (!c->have_scene) return fail(B200RT_ERR_STATE, "b200rt_texture_sample before b200rt_upload_scene");
+  if (n == 0) return B200RT_OK;
+  if (!uvp5 || !rgb) return fail(B200RT_ERR_INVALID, "NULL buffer");
+  CU(cudaSetDevice(c->device));
+  ScratchFree sf;
+  double *d_in = nullptr, *d_out = nullptr;
+  CU(cudaMalloc((void **)&d_in, n * 5 * sizeof(double)));
+  sf.p.push_back(d_in);
+  CU(cudaMalloc((void **)&d_out, n * 3 * sizeof(double)));
+  sf.p.push_back(d_out);
+  CU(cudaMemcpyAsync(d_in, uvp5, n * 5 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_texture<<<grid_for(c, n, 128, 16), 128, 0, c->stream>>>(c->S, tex, d_in, n, d_out);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(rgb, d_out, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200RT_OK;
+}
+
+int b200rt_generate_rays(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_end, double *rays7) {
+  if (!c || !rays7) return fail(B200RT_ERR_INVALID, "NULL argument");
+  if (!c->have_camera) return fail(B200RT_ERR_STATE, "b200rt_generate_rays before b200rt_set_camera");
+  if (spp_end < spp_begin || spp_begin < 0) return fail(B200RT_ERR_INVALID, "bad sample range [%d, %d)", spp_begin, spp_end);
+  const size_t n = (size_t)c->cam.image_width * c->cam.image_height * (size_t)(spp_end - spp_begin);
+  if (n == 0) return B200RT_OK;
+  CU(cudaSetDevice(c->device));
+  ScratchFree sf;
+  double *d = nullptr;
+  CU(cudaMalloc((void **)&d, n * 7 * sizeof(double)));
+  sf.p.push_back(d);
+  k_raygen<<<grid_for(c, n, 256, 8), 256, 0, c->stream>>>(make_camera(c->cam), seed, spp_begin, n, d);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(rays7, d, n * 7 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200RT_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+int ensure_wave(b200rt_ctx *c, uint32_t capacity, bool mirror) {
+  if (c->wave_capacity >= capacity && (!mirror || c->wave_mirror)) return B200RT_OK;
+  c->wave_mem.release();
+  c->wave_capacity = 0;
+  auto col = [&](void **p, size_t elem) { return c->wave_mem.alloc(p, (size_t)capacity * elem); };
+  for (int b = 0; b < 2; b++) {
+    PathBuf &P = c->pool[b];
+    double **dcols[10] = {&P.ox, &P.oy, &P.oz, &P.dx, &P.dy, &P.dz, &P.tm, &P.tx, &P.ty, &P.tz};
+    for (auto dc : dcols) CU(col((void **)dc, sizeof(double)));
+    CU(col((void **)&P.pixel, 4));
+    CU(col((void **)&P.sample, 4));
+    CU(col((void **)&P.bounce, 4));
+  }
+  CU(col((void **)&c->hits, sizeof(HitRef)));
+  c->recs = nullptr;
+  if (mirror) CU(col((void **)&c->recs, sizeof(Rec)));
+  for (int k = 0; k < B200_NQUEUES; k++) CU(col((void **)&c->queues.q[k], 4));
+  CU(c->wave_mem.alloc((void **)&c->ctl, sizeof(WaveCtl)));
+  c->wave_capacity = capacity;
+  c->wave_mirror = mirror;
+  return B200RT_OK;
+}
+
+template <bool MIRROR>
+void launch_shades(b200rt_ctx *c, cudaStream_t s, int grid, const PathBuf &cur, const PathBuf &nxt, double *accum, const WaveParams &wp) {
+#define SHADE(K) k_shade<K, MIRROR><<<grid, 128, 0, s>>>(c->ctl, c->S, cur, nxt, c->hits, c->recs, c->queues.q[K], accum, wp)
+  SHADE(B200_Q_MISS);
+  SHADE(B200RT_MAT_DIFFUSE_LIGHT);
+  SHADE(B200RT_MAT_LAMBERTIAN);
+  SHADE(B200RT_MAT_METAL);
+  SHADE(B200RT_MAT_DIELECTRIC);
+  SHADE(B200RT_MAT_GLOSS);
+  SHADE(B200RT_MAT_ISOTROPIC);
+#undef SHADE
+}
+
+} // namespace
+
+extern "C" {
+
+int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_end, double *d_rgb_sum, void *cuda_stream, b200rt_stats *stats) {
+  if (!c || !d_rgb_sum) return fail(B200RT_ERR_INVALID, "NULL argument");
+  if (!c->have_scene) return fail(B200RT_ERR_STATE, "render before b200rt_upload_scene");
+  if (!c->have_camera) return fail(B200RT_ERR_STATE, "render before b200rt_set_camera");
+  if (spp_end < spp_begin || spp_begin < 0) return fail(B200RT_ERR_INVALID, "bad sample range [%d, %d)", spp_begin, spp_end);
+  CU(cudaSetDevice(c->device));
+  cudaStream_t s = (cudaStream_t)cuda_stream;
+  const uint32_t npix = (uint32_t)c->cam.image_width * (uint32_t)c->cam.image_height;
+  const unsigned long long total = (unsigned long long)npix * (unsigned long long)(spp_end - spp_begin);
+  if (stats) std::memset(stats, 0, sizeof *stats);
+  if (total == 0) return B200RT_OK;
+  const bool mirror = c->traversal == B200RT_TRAVERSAL_MIRROR;
+  uint32_t capacity = c->wave_paths;
+  if (total < capacity) capacity = (uint32_t)((total + 31) & ~31ull);
+  int rc = ensure_wave(c, capacity, mirror);
+  if (rc != B200RT_OK) return rc;
+  if (mirror && (rc = prepare_mirror(c)) != B200RT_OK) return rc;
+  capacity = c->wave_capacity; // a larger pool from an earlier call is kept; use min(wave_paths, pool)
+  if (capacity > c->wave_paths) capacity = c->wave_paths;
+
+  WaveParams wp;
+  wp.seed = seed;
+  wp.npix = npix;
+  wp.width = (uint32_t)c->cam.image_width;
+  wp.spp_begin = spp_begin;
+  wp.max_depth = c->cam.max_depth;
+  wp.kill_zero = c->kill_zero;
+  wp.pad = 0;
+  const DevCamera cam = make_camera(c->cam);
+  const int g_gen = grid_for(c, capacity, 256, 8), g_ext = grid_for(c, capacity, 128, 16);
+
+  std::vector<cudaEvent_t> ext_events;
+  if (stats) CU(cudaEventRecord(c->ev0, s));
+  k_ctl_init<<<1, 1, 0, s>>>(c->ctl, total, capacity);
+  unsigned long long launches = 1, wave = 0, next_check = (total + capacity - 1) / capacity;
+  for (;;) {
+    const PathBuf &cur = c->pool[wave & 1], &nxt = c->pool[(wave & 1) ^ 1];
+    k_generate<<<g_gen, 256, 0, s>>>(c->ctl, cur, cam, wp, &c->ctl->nan_samples);
+    k_ctl_generated<<<1, 1, 0, s>>>(c->ctl);
+    if (stats) {
+      cudaEvent_t a, b;
+      CU(cudaEventCreate(&a));
+      CU(cudaEventCreate(&b));
+      ext_events.push_back(a);
+      ext_events.push_back(b);
+      CU(cudaEventRecord(a, s));
+    }
+    if (mirror)
+      k_extend<true><<<g_ext, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->recs, c->queues, wp);
+    else
+      k_extend<false><<<g_ext, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->recs, c->queues, wp);
+    if (stats) CU(cudaEventRecord(ext_events.back(), s));
+    if (mirror)
+      launch_shades<true>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
+    else
+      launch_shades<false>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
+    k_ctl_swap<<<1, 1, 0, s>>>(c->ctl);
+    launches += 4 + B200_NQUEUES;
+    wave++;
+    if (wave >= next_check) {
+      CU(cudaMemcpyAsync(c->h_ctl, c->ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, s));
+      CU(cudaStreamSynchronize(s));
+      const WaveCtl &h = *c->h_ctl;
+      if (h.n_cur == 0 && h.next_sample >= h.total_samples) break;
+      const unsigned long long left = h.total_samples - h.next_sample;
+      next_check = wave + (left > 0 ? std::max<unsigned long long>(1, left / capacity) : 2);
+    }
+  }
+  CU(cudaGetLastError());
+  if (stats) {
+    CU(cudaEventRecord(c->ev1, s));
+    CU(cudaEventSynchronize(c->ev1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    stats->gpu_ms = ms;
+    double ext = 0;
+    for (size_t k = 0; k + 1 < ext_events.size(); k += 2) {
+      float e = 0;
+      cudaEventElapsedTime(&e, ext_events[k], ext_events[k + 1]);
+      ext += e;
+    }
+    for (cudaEvent_t e : ext_events) cudaEventDestroy(e);
+    stats->extend_ms = ext;
+    stats->samples = total;
+    stats->rays = c->h_ctl->rays;
+    stats->nan_samples = c->h_ctl->nan_samples;
+    stats->kernel_launches = launches;
+  }
+  return B200RT_OK;
+}
+
+int b200rt_render(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_end, double *rgb_sum, b200rt_stats *stats) {
+  if (!c || !rgb_sum) return fail(B200RT_ERR_INVALID, "NULL argument");
+  if (!c->have_camera) return fail(B200RT_ERR_STATE, "render before b200rt_set_camera");
+  CU(cudaSetDevice(c->device));
+  const size_t elems = (size_t)c->cam.image_width * c->cam.image_height * 3;
+  if (c->accum_elems < elems) {
+    if (c->accum) cudaFree(c->accum);
+    c->accum = nullptr, c->accum_elems = 0;
+    CU(cudaMalloc((void **)&c->accum, elems * sizeof(double)));
+    c->accum_elems = elems;
+  }
+  CU(cudaMemsetAsync(c->accum, 0, elems * sizeof(double), c->stream));
+  int rc = b200rt_render_device(c, seed, spp_begin, spp_end, c->accum, c->stream, stats);
+  if (rc != B200RT_OK) return rc;
+  CU(cudaMemcpyAsync(rgb_sum, c->accum, elems * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (stats) {
+    stats->h2d_bytes = c->scene_h2d_bytes + sizeof(b200rt_camera);
+    stats->d2h_bytes = (double)(elems * sizeof(double));
+  }
+  return B200RT_OK;
+}
+
+int b200rt_finalize(b200rt_ctx *c, const double *rgb_sum, int total_spp, double *rgb_linear, int32_t *ppm_rgb) {
+  if (!c || !rgb_sum) return fail(B200RT_ERR_INVALID, "NULL argument");
+  if (!c->have_camera) return fail(B200RT_ERR_STATE, "finalize before b200rt_set_camera");
+  if (total_spp <= 0) return fail(B200RT_ERR_INVALID, "total_spp must be positive");
+  CU(cudaSetDevice(c->device));
+  const size_t n = (size_t)c->cam.image_width * c->cam.image_height * 3;
+  ScratchFree sf;
+  double *d_sum = nullptr, *d_lin = nullptr;
+  int32_t *d_ppm = nullptr;
+  CU(cudaMalloc((void **)&d_sum, n * sizeof(double)));
+  sf.p.push_back(d_sum);
+  CU(cudaMemcpyAsync(d_sum, rgb_sum, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if (rgb_linear) {
+    CU(cudaMalloc((void **)&d_lin, n * sizeof(double)));
+    sf.p.push_back(d_lin);
+  }
+  if (ppm_rgb) {
+    CU(cudaMalloc((void **)&d_ppm, n * sizeof(int32_t)));
+    sf.p.push_back(d_ppm);
+  }
+  k_finalize<<<grid_for(c, n, 256, 8), 256, 0, c->stream>>>(d_sum, n, (double)total_spp, d_lin, d_ppm);
+  CU(cudaGetLastError());
+  if (rgb_linear) CU(cudaMemcpyAsync(rgb_linear, d_lin, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (ppm_rgb) CU(cudaMemcpyAsync(ppm_rgb, d_ppm, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200RT_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,127 @@
+// shade_kernels.cuh — material-sorted shading, accumulation, and the batch entry points
+// (b200rt_trace / b200rt_generate_rays / b200rt_finalize kernels).
+#pragma once
+#include "wavefront.cuh"
+
+namespace b200 {
+
+DEV void accumulate(double *accum, uint32_t pixel, V c) { // image_[i*W+j] += sample, src/camera.h:167-169
+  if (c.x != 0.0) atomicAdd(accum + 3 * (size_t)pixel, c.x);
+  if (c.y != 0.0) atomicAdd(accum + 3 * (size_t)pixel + 1, c.y);
+  if (c.z != 0.0) atomicAdd(accum + 3 * (size_t)pixel + 2, c.z);
+}
+
+// One launch per queue.  KIND = b200rt_material_kind of every hit in the queue, or B200_Q_MISS.
+template <int KIND, bool MIRROR>
+__global__ void __launch_bounds__(128) k_shade(WaveCtl *c, DevScene S, PathBuf cur, PathBuf nxt, const HitRef *hits, const Rec *recs,
+                                                const uint32_t *queue, double *accum, WaveParams wp) {
+  const uint32_t n = c->q_count[KIND];
+  for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x) {
+    const uint32_t j = base + (threadIdx.x & 31);
+    bool survives = false;
+    Ray out_ray;
+    V T;
+    uint32_t pixel = 0, sample = 0, bounce = 0;
+    if (j < n) {
+      const uint32_t i = queue[j];
+      const Ray r = load_ray(cur, i);
+      T = v3(cur.tx[i], cur.ty[i], cur.tz[i]);
+      pixel = cur.pixel[i];
+      sample = cur.sample[i];
+      bounce = cur.bounce[i];
+      if (KIND == B200_Q_MISS) {
+        accumulate(accum, pixel, T * miss_color(S, r));
+      } else {
+        Rec rec;
+        if (MIRROR) {
+          rec = recs[i];
+        } else {
+          const HitRef h = hits[i];
+          finish_hit(S, S.entries[h.entry], r, h.t, rec);
+        }
+        const Stream st{wp.seed, pixel, sample};
+        const Scatter sc = shade_hit(S, rec, r, st, (int)bounce);
+        if (sc.ends) {
+          accumulate(accum, pixel, T * sc.value);
+        } else {
+          T = T * sc.value;
+          bounce += 1;
+          // ray_color(depth <= 0) returns 0 before tracing (src/camera.h:194-195); a path whose throughput
+          // is exactly 0 can only add 0 (optional cut, B200RT_OPT_KILL_ZERO_WEIGHT)
+          survives = (int)bounce < wp.max_depth && !(wp.kill_zero && T.x == 0.0 && T.y == 0.0 && T.z == 0.0);
+          out_ray = Ray{rec.p, sc.dir, r.tm};
+        }
+      }
+    }
+    const uint32_t pos = warp_append(&c->n_next, survives);
+    if (survives) {
+      store_ray(nxt, pos, out_ray);
+      nxt.tx[pos] = T.x, nxt.ty[pos] = T.y, nxt.tz[pos] = T.z;
+      nxt.pixel[pos] = pixel;
+      nxt.sample[pos] = sample;
+      nxt.bounce[pos] = bounce;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ batch entry points
+template <bool MIRROR>
+__global__ void __launch_bounds__(128) k_trace(DevScene S, const double *rays7, size_t n, double lo, double hi, uint64_t seed, int32_t *prim,
+                                                double *t, double *uv, uint8_t *front, double *p, double *normal) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const double *q = rays7 + 7 * i;
+    const Ray r{v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6]};
+    const Stream st{seed, (uint32_t)i, (uint32_t)(i >> 32)};
+    Rec rec;
+    bool ok;
+    if (MIRROR) {
+      MirrorCtx cx{&S, st, 0};
+      ok = mirror_hit(cx, (int)S.root, r, lo, hi, rec, 0);
+    } else {
+      const Best b = trace_closest(S, r, lo, hi, st, 0);
+      ok = b.entry >= 0;
+      if (ok) finish_hit(S, S.entries[b.entry], r, b.t, rec);
+    }
+    if (prim) prim[i] = ok ? rec.prim : -1;
+    if (t) t[i] = ok ? rec.t : 0.0;
+    if (uv) uv[2 * i] = ok ? rec.u : 0.0, uv[2 * i + 1] = ok ? rec.v : 0.0;
+    if (front) front[i] = ok && rec.front_face ? 1 : 0;
+    if (p) p[3 * i] = ok ? rec.p.x : 0.0, p[3 * i + 1] = ok ? rec.p.y : 0.0, p[3 * i + 2] = ok ? rec.p.z : 0.0;
+    if (normal) normal[3 * i] = ok ? rec.normal.x : 0.0, normal[3 * i + 1] = ok ? rec.normal.y : 0.0, normal[3 * i + 2] = ok ? rec.normal.z : 0.0;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_raygen(DevCamera cam, uint64_t seed, int spp_begin, size_t n, double *rays7) {
+  const size_t npix = (size_t)cam.c.image_width * cam.c.image_height;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t pixel = (uint32_t)(i % npix);
+    const uint32_t sample = (uint32_t)spp_begin + (uint32_t)(i / npix);
+    const Ray r = generate_ray(cam, Stream{seed, pixel, sample}, (int)(pixel / cam.c.image_width), (int)(pixel % cam.c.image_width));
+    double *o = rays7 + 7 * i;
+    o[0] = r.o.x, o[1] = r.o.y, o[2] = r.o.z, o[3] = r.d.x, o[4] = r.d.y, o[5] = r.d.z, o[6] = r.tm;
+  }
+}
+
+// pixel_color / spp and write_color (src/camera.h:169-170, src/color.h:16-36): gamma 2.2, int(255.999 c), unclamped
+__global__ void __launch_bounds__(256) k_finalize(const double *sum, size_t n, double spp, double *linear, int32_t *ppm) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const double c = sum[i] / spp;
+    if (linear) linear[i] = c;
+    if (ppm) {
+      const double g = c > 0 ? pow(c, 1 / 2.2) : 0.0;
+      const double v = 255.999 * g;
+      ppm[i] = (v > -2147483649.0 && v < 2147483648.0) ? (int32_t)v : (-2147483647 - 1); // NaN / out of range: what x86 cvttsd2si gives the reference
+    }
+  }
+}
+
+// texture::sample on a batch (parity entry for tests of the texture path)
+__global__ void __launch_bounds__(128) k_texture(DevScene S, int tex, const double *uvp5, size_t n, double *rgb) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const double *q = uvp5 + 5 * i;
+    const V c = tex_sample(S, tex, q[0], q[1], v3(q[2], q[3], q[4]));
+    rgb[3 * i] = c.x, rgb[3 * i + 1] = c.y, rgb[3 * i + 2] = c.z;
+  }
+}
+
+} // namespace b200

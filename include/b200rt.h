@@ -272,14 +272,23 @@ int b200rt_generate_rays(b200rt_ctx *ctx, uint64_t seed, int spp_begin, int spp_
  * sample count after combining ranges).  Host buffer; the device->host copy is part of the call. */
 int b200rt_render(b200rt_ctx *ctx, uint64_t seed, int spp_begin, int spp_end, double *rgb_sum, b200rt_stats *stats);
 
-/* Same, accumulating (+=) into a DEVICE buffer of W*H*3 doubles on `cuda_stream` (a cudaStream_t, may be 0);
- * asynchronous unless stats != NULL.  This is what the multi-GPU driver reduces with NCCL. */
+/* Same, accumulating (+=) into a DEVICE buffer of W*H*3 doubles with every kernel enqueued on `cuda_stream`
+ * (a cudaStream_t, may be 0).  The wave loop is driven from the host, so the call returns once the last wave
+ * has drained; the buffer is then complete on that stream.  This is what the multi-GPU driver reduces with NCCL. */
 int b200rt_render_device(b200rt_ctx *ctx, uint64_t seed, int spp_begin, int spp_end, double *d_rgb_sum,
                          void *cuda_stream, b200rt_stats *stats);
 
 /* Replaces: pixel_color /= spp and write_color (src/camera.h:169, src/color.h:16-36):
  * rgb_linear = rgb_sum / total_spp (may alias); ppm_rgb (may be NULL) gets int(255.999 * pow(c, 1/2.2)), unclamped. */
 int b200rt_finalize(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, double *rgb_linear, int32_t *ppm_rgb);
+
+/* Replaces: texture::sample(u, v, p) (src/texture.h:9) of texture row `tex` on a batch.
+ * uvp5 = n x {u, v, p[3]}, rgb = n x 3.  Host buffers. */
+int b200rt_texture_sample(b200rt_ctx *ctx, int tex, const double *uvp5, size_t n, double *rgb);
+
+/* sizeof() of the ABI structures as compiled into the library (0 scene_desc, 1 camera, 2 stats, 3 node, 4 material,
+ * 5 texture, 6 image, 7 volume, 8 value_noise, 9 bvh_info): lets foreign-language bindings check their mirrors. */
+size_t b200rt_abi_sizeof(int which);
 
 /* Introspection used by tests and the benchmark. */
 typedef struct b200rt_bvh_info {

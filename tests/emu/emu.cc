@@ -1,0 +1,157 @@
+// emu.cc — TEST INFRASTRUCTURE.  Runs the device functions of libb200rt.so's source (flatten.h, bvh_build.h,
+// traverse.cuh, mirror.cuh, intersect.cuh, shading.cuh, camera.cuh) on the CPU, one path at a time, so that the
+// CPU-only test tier can check the flattener, the BVH builder, the tie-break rule and the shading logic against
+// the oracle before any GPU time is spent.  It is NOT a fallback: nothing outside tests/ loads it, and the
+// wavefront kernels themselves (queues, compaction, atomics) are only exercised on a GPU.
+#include "bvh_build.h"
+#include "camera.cuh"
+#include "mirror.cuh"
+#include "shading.cuh"
+#include "traverse.cuh"
+
+using namespace b200;
+
+namespace {
+struct EmuScene {
+  DevScene S;
+  FlatScene fs;
+  BuiltBvh bvh;
+  std::vector<Entry> ordered;
+};
+} // namespace
+
+extern "C" {
+
+void *emu_scene_create(const b200rt_scene_desc *d, int leaf_size) {
+  auto *e = new EmuScene;
+  try {
+    Flattener fl(*d);
+    fl.run();
+    e->fs = std::move(fl.out);
+    e->bvh = BvhBuilder(e->fs.boxes, leaf_size).run();
+  } catch (const std::exception &ex) {
+    delete e;
+    return nullptr;
+  }
+  e->ordered.resize(e->fs.entries.size());
+  for (size_t k = 0; k < e->ordered.size(); k++) e->ordered[k] = e->fs.entries[e->bvh.perm[k]];
+  DevScene &S = e->S;
+  std::memset(&S, 0, sizeof S);
+  S.nodes = d->nodes, S.list_children = d->list_children, S.root = d->root;
+  S.spheres = d->spheres, S.sphere_mat = d->sphere_mat, S.quads = d->quads, S.quad_mat = d->quad_mat, S.tris = d->tris, S.tri_mat = d->tri_mat;
+  S.volumes = d->volumes, S.materials = d->materials, S.textures = d->textures, S.images = d->images, S.image_bytes = d->image_bytes;
+  S.perlin_vec = d->perlin_vec, S.perlin_perm = d->perlin_perm, S.value_noise = d->value_noise, S.value_lattice = d->value_lattice;
+  S.light_kind = d->light_kind, S.light_index = d->light_index, S.background_tex = d->background_tex;
+  S.bvh = e->bvh.nodes.data(), S.bvh_root = e->bvh.root, S.n_bvh_nodes = (uint32_t)e->bvh.nodes.size();
+  S.entries = e->ordered.data(), S.bentries = e->fs.bentries.data(), S.vol_inst = e->fs.vol_inst.data();
+  S.chain_ops = e->fs.chain_ops.data(), S.chains = e->fs.chains.data(), S.n_entries = (uint32_t)e->ordered.size();
+  S.has_volumes = e->fs.has_volumes;
+  return e;
+}
+void emu_scene_destroy(void *h) { delete static_cast<EmuScene *>(h); }
+void emu_scene_info(void *h, uint32_t *out6) {
+  auto *e = static_cast<EmuScene *>(h);
+  out6[0] = (uint32_t)e->bvh.nodes.size(), out6[1] = e->bvh.n_leaves, out6[2] = (uint32_t)e->ordered.size(), out6[3] = e->bvh.max_depth;
+  out6[4] = (uint32_t)e->fs.graph_depth, out6[5] = (uint32_t)e->fs.chains.size();
+}
+
+int emu_trace(void *h, int mirror, const double *rays7, size_t n, double lo, double hi, uint64_t seed, int32_t *prim, double *t, double *uv,
+              uint8_t *front, double *p, double *normal) {
+  const DevScene &S = static_cast<EmuScene *>(h)->S;
+  for (size_t i = 0; i < n; i++) {
+    const double *q = rays7 + 7 * i;
+    const Ray r{v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6]};
+    const Stream st{seed, (uint32_t)i, (uint32_t)(i >> 32)};
+    Rec rec;
+    std::memset(&rec, 0, sizeof rec);
+    bool ok;
+    if (mirror) {
+      MirrorCtx cx{&S, st, 0};
+      ok = mirror_hit(cx, (int)S.root, r, lo, hi, rec, 0);
+    } else {
+      const Best b = trace_closest(S, r, lo, hi, st, 0);
+      ok = b.entry >= 0;
+      if (ok) finish_hit(S, S.entries[b.entry], r, b.t, rec);
+    }
+    if (prim) prim[i] = ok ? rec.prim : -1;
+    if (t) t[i] = ok ? rec.t : 0.0;
+    if (uv) uv[2 * i] = ok ? rec.u : 0.0, uv[2 * i + 1] = ok ? rec.v : 0.0;
+    if (front) front[i] = ok && rec.front_face ? 1 : 0;
+    if (p) p[3 * i] = ok ? rec.p.x : 0.0, p[3 * i + 1] = ok ? rec.p.y : 0.0, p[3 * i + 2] = ok ? rec.p.z : 0.0;
+    if (normal) normal[3 * i] = ok ? rec.normal.x : 0.0, normal[3 * i + 1] = ok ? rec.normal.y : 0.0, normal[3 * i + 2] = ok ? rec.normal.z : 0.0;
+  }
+  return 0;
+}
+
+int emu_generate_rays(const b200rt_camera *c, uint64_t seed, int spp_begin, int spp_end, double *rays7) {
+  const DevCamera cam = make_camera(*c);
+  const size_t npix = (size_t)c->image_width * c->image_height;
+  for (size_t i = 0; i < npix * (size_t)(spp_end - spp_begin); i++) {
+    const uint32_t pixel = (uint32_t)(i % npix), sample = (uint32_t)spp_begin + (uint32_t)(i / npix);
+    const Ray r = generate_ray(cam, Stream{seed, pixel, sample}, (int)(pixel / c->image_width), (int)(pixel % c->image_width));
+    double *o = rays7 + 7 * i;
+    o[0] = r.o.x, o[1] = r.o.y, o[2] = r.o.z, o[3] = r.d.x, o[4] = r.d.y, o[5] = r.d.z, o[6] = r.tm;
+  }
+  return 0;
+}
+
+int emu_texture_sample(void *h, int tex, const double *uvp5, size_t n, double *rgb) {
+  const DevScene &S = static_cast<EmuScene *>(h)->S;
+  for (size_t i = 0; i < n; i++) {
+    const double *q = uvp5 + 5 * i;
+    const V c = tex_sample(S, tex, q[0], q[1], v3(q[2], q[3], q[4]));
+    rgb[3 * i] = c.x, rgb[3 * i + 1] = c.y, rgb[3 * i + 2] = c.z;
+  }
+  return 0;
+}
+
+// per-sample radiance, one path at a time, with the update rule of k_shade (shade_kernels.cuh)
+int emu_render(void *h, int mirror, const b200rt_camera *c, uint64_t seed, int spp_begin, int spp_end, int kill_zero, double *rgb_sum,
+               double *per_sample, uint64_t *rays_out) {
+  const DevScene &S = static_cast<EmuScene *>(h)->S;
+  const DevCamera cam = make_camera(*c);
+  const size_t npix = (size_t)c->image_width * c->image_height;
+  uint64_t rays = 0;
+  for (int k = spp_begin; k < spp_end; k++)
+    for (uint32_t pixel = 0; pixel < npix; pixel++) {
+      const Stream st{seed, pixel, (uint32_t)k};
+      Ray r = generate_ray(cam, st, (int)(pixel / c->image_width), (int)(pixel % c->image_width));
+      V T = v3(1, 1, 1), L = v3(0, 0, 0);
+      if (!(isnan(r.d.x) || isnan(r.d.y) || isnan(r.d.z))) {
+        for (int bounce = 0; bounce < c->max_depth; bounce++) {
+          rays++;
+          Rec rec;
+          bool ok;
+          if (mirror) {
+            MirrorCtx cx{&S, st, bounce};
+            ok = mirror_hit(cx, (int)S.root, r, 0.001, B200_INF, rec, 0);
+          } else {
+            const Best b = trace_closest(S, r, 0.001, B200_INF, st, bounce);
+            ok = b.entry >= 0;
+            if (ok) finish_hit(S, S.entries[b.entry], r, b.t, rec);
+          }
+          if (!ok) {
+            L = T * miss_color(S, r);
+            break;
+          }
+          const Scatter sc = shade_hit(S, rec, r, st, bounce);
+          if (sc.ends) {
+            L = T * sc.value;
+            break;
+          }
+          T = T * sc.value;
+          if (kill_zero && T.x == 0.0 && T.y == 0.0 && T.z == 0.0) break;
+          r = Ray{rec.p, sc.dir, r.tm};
+        }
+      }
+      const double cc[3] = {L.x, L.y, L.z};
+      for (int q = 0; q < 3; q++) {
+        if (rgb_sum) rgb_sum[3 * (size_t)pixel + q] += cc[q];
+        if (per_sample) per_sample[((size_t)(k - spp_begin) * npix + pixel) * 3 + q] = cc[q];
+      }
+    }
+  if (rays_out) *rays_out = rays;
+  return 0;
+}
+
+} // extern "C"

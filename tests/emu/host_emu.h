@@ -1,0 +1,28 @@
+// host_emu.h — TEST INFRASTRUCTURE.  Minimal stand-ins for the CUDA built-ins used by the device FUNCTIONS of
+// cpu-ray-tracing-implementation_b200/csrc (not the kernels), so that tests/emu/emu.cc can execute the very same
+// traversal / intersection / shading source on the CPU of a box without a GPU.  Never part of libb200rt.so.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#define __host__
+#define __device__
+#define __forceinline__ inline
+#define __noinline__
+#define __align__(n) alignas(n)
+struct alignas(16) double2 {
+  double x, y;
+};
+struct alignas(8) int2 {
+  int x, y;
+};
+struct alignas(16) int4 {
+  int x, y, z, w;
+};
+template <class T> inline T __ldg(const T *p) { return *p; }
+inline double __longlong_as_double(long long v) {
+  double d;
+  std::memcpy(&d, &v, 8);
+  return d;
+}
+using std::isnan;
