@@ -1,0 +1,233 @@
+"""-m gpu: the CUDA path (libb200rt.so through its C ABI) against the oracle and the reference's golden vectors.
+
+Tolerances: primitive ids, front_face: bit-exact.  t, p, normal, quad u/v: bit-exact (same binary64 operations in the
+same order, no FMA).  sphere u/v and fisheye rays go through acos/atan2/asin/sin/cos, where CUDA's libm and glibc may
+differ in the last place: 4 ulp.  Radiance per sample: 1e-9 relative on >= 99.5 % of samples (a last-place difference
+in a sampled direction can flip a later branch on a few paths); images: RMSE < 1e-3 and mean within 0.5 %.
+"""
+import numpy as np
+import pytest
+from conftest import ALL_SCENES, CONFIG_SCENES, VOLUME_SCENES, abi, golden, pkg, same
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = pkg.backend.Context(0)
+    yield c
+    c.close()
+
+
+def ulp_close(a, b, ulps):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    tol = ulps * np.spacing(np.maximum(np.abs(a), np.abs(b)))
+    return (np.abs(a - b) <= tol) | (np.isnan(a) & np.isnan(b))
+
+
+def check_records(name, out, ref, keep):
+    for k in ("prim", "front", "t", "p", "normal"):
+        ok = same(out[k][keep], ref[k][keep])
+        assert ok.all(), f"{name}: {k} differs on {(~ok).sum()} of {keep.sum()} rays"
+    ok = ulp_close(out["uv"][keep], ref["uv"][keep], 4) | (np.abs(out["uv"][keep] - ref["uv"][keep]) < 1e-15)
+    assert ok.all(), f"{name}: uv differs on {(~ok).sum()} rays"
+
+
+@pytest.mark.parametrize("mode", [abi.TRAVERSAL_FAST, abi.TRAVERSAL_MIRROR])
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_hits_vs_reference_golden(ctx, name, mode):
+    """b200rt_trace on the golden ray batch == the reference's own <world>.hit records."""
+    g = golden(name)
+    ctx.set_option(abi.OPT_TRAVERSAL, mode)
+    ctx.upload_scene(g.scene)
+    out = ctx.trace(g["trace_rays"], seed=99)
+    ctx.set_option(abi.OPT_TRAVERSAL, abi.TRAVERSAL_FAST)
+    ref = {k: g["trace_" + k] for k in ("prim", "t", "uv", "front", "p", "normal")}
+    keep = np.ones(len(out["prim"]), bool)
+    if name in VOLUME_SCENES:
+        vol = np.array(sorted(g.volume_prims()))
+        keep = ~np.isin(out["prim"], vol) & ~np.isin(ref["prim"], vol)
+    check_records(name, out, ref, keep)
+
+
+@pytest.mark.parametrize("mode", [abi.TRAVERSAL_FAST, abi.TRAVERSAL_MIRROR])
+@pytest.mark.parametrize("name", sorted(VOLUME_SCENES))
+def test_volume_hits_vs_oracle(ctx, name, mode, build_oracle):
+    """Same Philox free-flight draws on both sides: volume hits are comparable too (log() may differ in the last place)."""
+    g = golden(name)
+    ctx.set_option(abi.OPT_TRAVERSAL, mode)
+    ctx.upload_scene(g.scene)
+    out = ctx.trace(g["trace_rays"], seed=99)
+    ctx.set_option(abi.OPT_TRAVERSAL, abi.TRAVERSAL_FAST)
+    ref = build_oracle.trace(g.scene, g["trace_rays"], seed=99)
+    assert (out["prim"] == ref["prim"]).mean() > 0.9999
+    m = out["prim"] == ref["prim"]
+    assert np.allclose(out["t"][m], ref["t"][m], rtol=1e-12, atol=0)
+    assert np.isin(ref["prim"], np.array(sorted(g.volume_prims()))).sum() > 20
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_camera_rays_vs_oracle(ctx, name, build_oracle):
+    g = golden(name)
+    ctx.set_camera(g.cam_small)
+    rays = ctx.generate_rays(31337, 1, 3)
+    ref = build_oracle.generate_rays(g.cam_small, 31337, 1, 3)
+    if g.cam_small.mode == abi.CAM_FISHEYE:
+        assert (np.isnan(rays) == np.isnan(ref)).all()
+        assert np.allclose(rays, ref, rtol=1e-13, atol=1e-15, equal_nan=True)
+    else:
+        assert same(rays, ref).all()
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_textures_vs_reference_golden(ctx, name):
+    g = golden(name)
+    ctx.upload_scene(g.scene)
+    rows = g["tex_rows"]
+    kinds = g.scene.textures["kind"]
+    for t in np.unique(rows):
+        rgb = ctx.texture_sample(int(t), g["tex_uvp"][rows == t])
+        ref = g["tex_rgb"][rows == t]
+        if kinds[t] in (abi.TEX_PERLIN, abi.TEX_WORLEY, abi.TEX_VORONOI):  # sin() inside: last-place differences allowed
+            if kinds[t] == abi.TEX_PERLIN:
+                assert np.allclose(rgb, ref, rtol=0, atol=1e-12), f"{name}: texture {t}"
+            else:  # fract(sin(x) * 43758.5453) amplifies a 1-ulp difference of sin() by ~1e5, and a nearest-cell flip is possible
+                assert (np.abs(rgb - ref) < 1e-8).mean() > 0.98, f"{name}: texture {t}"
+        else:
+            assert same(rgb, ref).all(), f"{name}: texture {t}"
+
+
+def render_pair(ctx, oracle, g, seed, spp, mode=abi.TRAVERSAL_FAST, kill_zero=0):
+    ctx.set_option(abi.OPT_TRAVERSAL, mode)
+    ctx.set_option(abi.OPT_KILL_ZERO_WEIGHT, kill_zero)
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(g.cam_small)
+    img, st = ctx.render(seed, 0, spp)
+    ctx.set_option(abi.OPT_TRAVERSAL, abi.TRAVERSAL_FAST)
+    ctx.set_option(abi.OPT_KILL_ZERO_WEIGHT, 1)
+    ref = oracle.render(g.scene, g.cam_small, seed, 0, spp, threads=0)
+    return img, st, ref
+
+
+@pytest.mark.parametrize("name", [s for s in ALL_SCENES if s != "motion_ball"])
+def test_render_matches_oracle_sample_for_sample(ctx, name, build_oracle):
+    """Same draws on both sides => the spp-sample image itself must agree, not just its expectation."""
+    g = golden(name)
+    spp = 8
+    img, st, ref = render_pair(ctx, build_oracle, g, 4711, spp)
+    a, b = img / spp, ref["sum"] / spp
+    fin = np.isfinite(a) & np.isfinite(b)
+    assert fin.mean() > 0.995
+    close = np.abs(a - b) <= 1e-9 * np.maximum(np.abs(b), 1e-3)
+    assert close[fin].mean() > 0.995, f"{name}: only {close[fin].mean():.4f} of pixels agree to 1e-9"
+    rmse = np.sqrt(((a - b)[fin] ** 2).mean())
+    assert rmse < 1e-3 * max(1.0, np.abs(b[fin]).max()), f"{name}: rmse {rmse}"
+    assert abs(a[fin].mean() - b[fin].mean()) <= 0.005 * abs(b[fin].mean()) + 1e-12
+    assert st["samples"] == ref["stats"]["samples"] and st["nan_samples"] == ref["stats"]["nan_samples"]
+    assert abs(int(st["rays"]) - int(ref["stats"]["rays"])) <= 0.002 * ref["stats"]["rays"] + 2, (st["rays"], ref["stats"]["rays"])
+
+
+@pytest.mark.parametrize("name", ["cornell", "rtnw", "fox", "cornell_volume"])
+def test_render_mirror_mode_matches_oracle(ctx, name, build_oracle):
+    g = golden(name)
+    spp = 4
+    img, st, ref = render_pair(ctx, build_oracle, g, 99, spp, mode=abi.TRAVERSAL_MIRROR)
+    a, b = img / spp, ref["sum"] / spp
+    fin = np.isfinite(a) & np.isfinite(b)
+    close = np.abs(a - b) <= 1e-9 * np.maximum(np.abs(b), 1e-3)
+    assert close[fin].mean() > 0.995
+
+
+@pytest.mark.parametrize("name", CONFIG_SCENES)
+def test_converged_image_vs_reference(ctx, name):
+    """North-star image criterion against the reference's OWN render (golden sums): per-pixel z-scores consistent with
+    Monte-Carlo error, image mean within 0.5 % (+ standard error)."""
+    from conftest import z_scores
+
+    g = golden(name)
+    n_ref = int(g["ref_spp"])
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(g.cam_small)
+    H, W = g.cam_small.image_height, g.cam_small.image_width
+    n = 4 * n_ref
+    s = np.zeros((H, W, 3))
+    sq = np.zeros((H, W, 3))
+    for k in range(0, n, n // 16):  # 16 batches give a per-pixel variance estimate of batch means
+        part, _ = ctx.render(5, k, k + n // 16)
+        s += part
+        sq += part**2 / (n // 16)
+    fin = np.isfinite(s) & np.isfinite(g["ref_sum"])
+    mean_g, mean_r = s / n, g["ref_sum"] / n_ref
+    var_r = np.maximum(g["ref_sumsq"] / n_ref - mean_r**2, 0)
+    var_g = np.maximum(sq / n - mean_g**2, 0)  # variance of a single sample, from batch sums
+    var = np.where(fin, 0.5 * (var_r + var_g), 0)
+    se = np.sqrt(var / n + var / n_ref)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        z = np.where((se > 0) & fin, (mean_g - mean_r) / se, 0)
+    assert np.sqrt((z**2).mean()) < 1.3 and np.abs(z).max() < 7, (np.sqrt((z**2).mean()), np.abs(z).max())
+    tot_g, tot_r = mean_g[fin].mean(), mean_r[fin].mean()
+    se_tot = np.sqrt((var / n + var / n_ref)[fin].sum()) / fin.sum()
+    assert abs(tot_g - tot_r) <= 0.005 * abs(tot_r) + 5 * se_tot
+
+
+def test_sample_ranges_add_up_and_wave_size_is_irrelevant(ctx):
+    """Properties the multi-GPU split relies on: render[0,b) == render[0,a) + render[a,b) and the result does not depend
+    on the wave size (only fp64 atomic summation order differs)."""
+    g = golden("rtow")
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(g.cam_small)
+    whole, st = ctx.render(1234, 0, 24)
+    a, _ = ctx.render(1234, 0, 10)
+    b, _ = ctx.render(1234, 10, 24)
+    assert np.allclose(whole, a + b, rtol=1e-12, atol=1e-12)
+    ctx.set_option(abi.OPT_WAVE_PATHS, 4096)
+    small, st2 = ctx.render(1234, 0, 24)
+    ctx.set_option(abi.OPT_WAVE_PATHS, 1 << 22)
+    assert np.allclose(whole, small, rtol=1e-12, atol=1e-12)
+    assert st["rays"] == st2["rays"] and st["samples"] == st2["samples"] == 24 * g.cam_small.image_width * g.cam_small.image_height
+
+
+def test_white_furnace_known_answer(ctx):
+    """White Sphere (src/main.cc:500-510): albedo-1 metal under a white background: every sample is 1 unless the path
+    runs out of depth re-hitting the sphere."""
+    g = golden("white_sphere")
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(g.cam_small)
+    img, st = ctx.render(3, 0, 64)
+    m = img / 64
+    assert m.max() <= 1.0 + 1e-12 and m.mean() > 0.99
+
+
+def test_finalize_matches_write_color(ctx):
+    g = golden("cornell")
+    ctx.set_camera(g.cam_small)
+    H, W = g.cam_small.image_height, g.cam_small.image_width
+    rng = np.random.RandomState(0)
+    s = rng.rand(H, W, 3) * 40
+    s[0, 0, 0] = np.nan
+    s[0, 1, 1] = -3.0
+    s[0, 2, 2] = 1e300
+    lin, ppm = ctx.finalize(s, 16, want_ppm=True)
+    assert same(lin, s / 16).all()
+    c = s / 16
+    with np.errstate(invalid="ignore"):
+        expect = np.where(c > 0, np.power(np.where(c > 0, c, 1.0), 1 / 2.2), 0.0) * 255.999
+    big = ~(np.abs(expect) < 2**31)
+    ref = np.where(big, -(2**31), np.where(big, 0, expect).astype(np.int64))
+    assert (np.abs(ppm.astype(np.int64) - ref) <= 1).all() and (ppm[big] == -(2**31)).all()
+
+
+def test_errors_are_loud(ctx):
+    from conftest import Scene
+
+    c2 = pkg.backend.Context(0)
+    with pytest.raises(pkg.backend.B200RTError):
+        c2.trace(np.zeros((4, 7)))  # no scene yet
+    bad = Scene.load(golden("cornell").z)
+    bad.quad_mat = bad.quad_mat.copy()
+    bad.quad_mat[0] = 999
+    with pytest.raises(pkg.backend.B200RTError):
+        c2.upload_scene(bad)
+    with pytest.raises(pkg.backend.B200RTError):
+        pkg.backend.Context(99)
+    c2.close()
