@@ -91,8 +91,11 @@ def test_textures_vs_reference_golden(ctx, name):
         if kinds[t] in (abi.TEX_PERLIN, abi.TEX_WORLEY, abi.TEX_VORONOI):  # sin() inside: last-place differences allowed
             if kinds[t] == abi.TEX_PERLIN:
                 assert np.allclose(rgb, ref, rtol=0, atol=1e-12), f"{name}: texture {t}"
-            else:  # fract(sin(x) * 43758.5453) amplifies a 1-ulp difference of sin() by ~1e5, and a nearest-cell flip is possible
+            elif kinds[t] == abi.TEX_WORLEY:  # fract(sin(x) * 43758.5453) amplifies a 1-ulp difference of sin() by ~1e5, and a nearest-cell flip is possible
                 assert (np.abs(rgb - ref) < 1e-8).mean() > 0.98, f"{name}: texture {t}"
+            else:  # voronoi hashes the hashed position again (src/noise.h:193): a last-place sin() difference is amplified twice, ~1e-16 * 43758 * 312 * 43758
+                assert (np.abs(rgb - ref) < 1e-3).mean() > 0.98, f"{name}: texture {t}"
+                assert (np.abs(rgb - ref) < 1e-8).mean() > 0.3, f"{name}: texture {t}"
         else:
             assert same(rgb, ref).all(), f"{name}: texture {t}"
 
