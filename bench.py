@@ -146,6 +146,10 @@ def run_ours(args):
     H, W = cam.image_height, cam.image_width
     ctx = pkg.backend.Context(local)
     ctx.set_option(abi.OPT_WAVE_PATHS, args.wave)
+    if args.refill:
+        ctx.set_option(abi.OPT_REFILL_LANES, args.refill)
+    if args.leaf:
+        ctx.set_option(abi.OPT_BVH_LEAF_SIZE, args.leaf)
     ctx.upload_scene(scene)
     ctx.set_camera(cam)
     accum = torch.zeros(H * W * 3, dtype=torch.float64, device="cuda")
@@ -245,6 +249,8 @@ if __name__ == "__main__":
     ap.add_argument("--wave", type=int, default=1 << 22, help="paths resident per wave")
     ap.add_argument("--seed", type=int, default=0x5EED)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--refill", type=int, default=0, help="tuning: idle lanes per warp that trigger a ray fetch in the persistent extend kernel")
+    ap.add_argument("--leaf", type=int, default=0, help="tuning: max primitives per BVH leaf")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)

@@ -59,6 +59,7 @@ struct b200rt_ctx {
   uint32_t wave_paths = 1u << 22;
   int kill_zero = 1;
   int bvh_leaf = 2;
+  int refill_lanes = 32;
   // scene
   bool have_scene = false, have_camera = false;
   DevMem scene_mem;
@@ -209,6 +210,10 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     c->bvh_leaf = (int)value; // takes effect at the next b200rt_upload_scene
     return B200RT_OK;
   case B200RT_OPT_SMEM_NODES: return B200RT_OK; // reserved
+  case B200RT_OPT_REFILL_LANES:
+    if (!(value >= 1 && value <= 32)) return fail(B200RT_ERR_INVALID, "refill lanes must be in [1, 32]");
+    c->refill_lanes = (int)value;
+    return B200RT_OK;
   }
   return fail(B200RT_ERR_INVALID, "unknown option %d", option);
 }
@@ -283,6 +288,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   S.n_bvh_nodes = (uint32_t)bvh.nodes.size();
   S.n_entries = (uint32_t)ordered.size();
   S.has_volumes = fs.has_volumes ? 1 : 0;
+  for (int k = 0; k < 3; k++) S.bound[k] = bvh.bound[k];
   CU(cudaStreamSynchronize(c->stream)); // host vectors go out of scope
   c->S = S;
   c->bvh_info.n_nodes = (uint32_t)bvh.nodes.size();
@@ -497,7 +503,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   wp.spp_begin = spp_begin;
   wp.max_depth = c->cam.max_depth;
   wp.kill_zero = c->kill_zero;
-  wp.pad = 0;
+  wp.refill = c->refill_lanes;
   const DevCamera cam = make_camera(c->cam);
   const int g_gen = grid_for(c, capacity, 256, 8), g_ext = grid_for(c, capacity, 128, 16);
 
@@ -520,7 +526,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     if (mirror)
       k_extend<true><<<g_ext, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->recs, c->queues, wp);
     else
-      k_extend<false><<<g_ext, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->recs, c->queues, wp);
+      k_extend_persistent<<<c->sm_count * 4, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->queues, wp);
     if (stats) CU(cudaEventRecord(ext_events.back(), s));
     if (mirror)
       launch_shades<true>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);

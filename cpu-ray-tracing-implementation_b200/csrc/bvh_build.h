@@ -19,6 +19,7 @@ struct BuiltBvh {
   int32_t root = B200_EMPTY_ROOT;
   uint32_t n_leaves = 0, max_depth = 0;
   double sah_cost = 0, build_ms = 0;
+  double bound[3] = {0, 0, 0}; // max |finite fp32 plane| per axis
 };
 
 class BvhBuilder {
@@ -54,8 +55,25 @@ private:
   BuiltBvh out_;
   double cost_acc_ = 0, root_area_ = 0;
 
-  static void set_box(double dst[6], const Box &b) {
-    dst[0] = b.lo[0], dst[1] = b.hi[0], dst[2] = b.lo[1], dst[3] = b.hi[1], dst[4] = b.lo[2], dst[5] = b.hi[2];
+  static float round_down(double x) {
+    float f = (float)x;
+    if ((double)f > x) f = std::nextafterf(f, -INFINITY);
+    return f;
+  }
+  static float round_up(double x) {
+    float f = (float)x;
+    if ((double)f < x) f = std::nextafterf(f, INFINITY);
+    return f;
+  }
+  void set_box(float dst[6], const Box &b) {
+    for (int k = 0; k < 3; k++) {
+      dst[2 * k] = round_down(b.lo[k]);
+      dst[2 * k + 1] = round_up(b.hi[k]);
+      for (int e = 0; e < 2; e++) {
+        const double a = std::fabs((double)dst[2 * k + e]);
+        if (std::isfinite(a) && a > out_.bound[k]) out_.bound[k] = a;
+      }
+    }
   }
 
   int32_t make_leaf(uint32_t begin, uint32_t end, uint32_t depth, const Box &b) {

@@ -44,14 +44,16 @@ struct __align__(16) VolInst {
   int32_t bfirst, bcount; // boundary entries (closest boundary hit = min t over them)
 };
 
-// BVH2 node, 128 bytes = one L2 line = eight 128-bit loads.  Boxes are padded outward at build time.
+// BVH2 node, 64 bytes = four 128-bit loads: both children's boxes as binary32 planes rounded OUTWARD from the
+// (already padded) binary64 boxes.  The box test is a conservative filter only (traverse.cuh); every accepted
+// leaf is then tested in binary64, so the fp32 planes never influence a returned t or id.
 struct __align__(16) BvhNode {
-  double lbox[6]; // left child  {x0,x1,y0,y1,z0,z1}
-  double rbox[6]; // right child
+  float lbox[6]; // left child  {x0,x1,y0,y1,z0,z1}
+  float rbox[6]; // right child
   int32_t left, right; // >= 0: inner node index; < 0: leaf, ~ref = first_entry << 3 | (count - 1)
-  int32_t pad[6];
+  int32_t pad[2];
 };
-static_assert(sizeof(BvhNode) == 128, "BvhNode must be one 128-byte line");
+static_assert(sizeof(BvhNode) == 64, "BvhNode must be half a 128-byte line");
 static_assert(sizeof(Entry) == 16 && sizeof(VolInst) == 16 && sizeof(ChainOp) == 32, "layout");
 
 #define B200_EMPTY_ROOT (-2147483647 - 1)
@@ -88,6 +90,7 @@ struct DevScene {
   const Chain *chains;
   uint32_t n_entries;
   int32_t has_volumes;
+  double bound[3]; // max |finite box plane| per axis over the whole BVH: sizes the fp32 error margin of the box test
 };
 
 // What extend leaves behind for shade: enough to rebuild the full hit_record deterministically.

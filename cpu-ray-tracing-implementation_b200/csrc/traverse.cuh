@@ -1,18 +1,25 @@
 // traverse.cuh — closest-hit search over the compacted BVH2: what replaces bvh_node::hit (src/bvh_node.h:49-59)
 // and aabb::hit (src/aabb.h:28-33, 45-69) on the wavefront path.
 //
-//   * one 128-byte node fetch (eight 128-bit read-only loads) tests both children;
-//   * slab test on precomputed reciprocals; NaN-safe min/max (fmin/fmax drop NaNs, so a zero direction
-//     component with the origin on a slab plane does not poison the interval);
-//   * near child first, far child on a short per-thread stack;
-//   * a candidate replaces the current best iff  t < best.t  or  (t == best.t and order > best.order):
-//     the reference's closed-interval "last visited wins" rule expressed without its visiting order.
+// Two precisions, two jobs:
+//   * BOX TESTS are a conservative binary32 filter.  One 64-byte node fetch (four 128-bit read-only loads)
+//     holds both children's planes, rounded outward at build time.  Per plane one FFMA
+//         t = plane * (1/d) - (o/d -/+ E)
+//     where o/d is formed in binary64 and E bounds every rounding of the fp32 evaluation
+//     (E = 2^-23 M / |d| per axis, M = largest |plane| of the scene), plus 4 ulp relative slack on the
+//     final interval.  A box the exact ray touches is never rejected; a few untouched boxes are accepted.
+//   * LEAF TESTS are binary64 in the reference's operation order (intersect.cuh), so t / p / normal and the
+//     winning primitive are bit-identical to the reference whatever the filter let through.
+// A candidate replaces the current best iff  t < best.t  or  (t == best.t and order > best.order): the
+// reference's closed-interval "last visited wins" rule expressed without its visiting order,
+// which is what makes the result independent of the tree we traverse.
 #pragma once
 #include "intersect.cuh"
 
 namespace b200 {
 
 #define B200_STACK 64
+#define B200_DONE B200_EMPTY_ROOT
 
 struct Best {
   double t;
@@ -20,16 +27,65 @@ struct Best {
   uint32_t order;
 };
 
-DEV void slab2(const double *bx, const V &o, const V &inv, double lo, double hi, double &tn, double &tf) {
-  double x0, x1, y0, y1, z0, z1;
-  ld2(bx, x0, x1);
-  ld2(bx + 2, y0, y1);
-  ld2(bx + 4, z0, z1);
-  const double ax = (x0 - o.x) * inv.x, bx_ = (x1 - o.x) * inv.x;
-  const double ay = (y0 - o.y) * inv.y, by = (y1 - o.y) * inv.y;
-  const double az = (z0 - o.z) * inv.z, bz = (z1 - o.z) * inv.z;
-  tn = fmax(fmax(fmin(ax, bx_), fmin(ay, by)), fmax(fmin(az, bz), lo));
-  tf = fmin(fmin(fmax(ax, bx_), fmax(ay, by)), fmin(fmax(az, bz), hi));
+// Per-ray constants of the fp32 box filter.  The filter works in a rescaled parameter t' = t * tsc, d' = d / tsc, with tsc the
+// power of two just below the largest direction component (d' lands in [1, 2)): exact, and it keeps rays whose direction is
+// uniformly tiny or huge (t of 1e30 and beyond is legitimate in the reference) inside fp32 range.
+struct RaySetup {
+  float ix, iy, iz; // 1/(d sc), clamped to +-2^100 (a zero component behaves like an almost-parallel ray)
+  float c0x, c1x;   // what is subtracted from x0 * ix and x1 * ix: o/(d sc) with the margin on the safe side
+  float c0y, c1y;
+  float c0z, c1z;
+  double tsc;
+};
+
+DEV void setup_axis(double o, double d, double M, float &inv_f, float &c0, float &c1) {
+  const double B = 1.2676506002282294e30; // 2^100
+  double inv = 1.0 / d;
+  if (inv > B) inv = B;
+  if (inv < -B) inv = -B;
+  const double ainv = fabs(inv);
+  // what the filter cannot bound (NaN anywhere, |o| beyond 2^26): plane * 0 -+ inf = this axis accepts every box
+  if (!(ainv >= 0.25) || !(fabs(o) <= 6.7108864e7)) {
+    inv_f = 0.0f;
+    c0 = __int_as_float(0x7f800000); // plane*0 - (+inf) = -inf
+    c1 = -c0;                        // plane*0 - (-inf) = +inf
+    return;
+  }
+  const double oi = o * inv;
+  const double E = 1.1920928955078125e-7 * M * ainv + 1e-37; // 2^-23 = 2 ulp32: inv_f is 1/d to half an ulp, |plane| <= M; o/d itself is rounded on the safe side below
+  const float cn = __double2float_ru(oi + E); // near planes: t comes out too small, never too large
+  const float cf = __double2float_rd(oi - E); // far planes: too large, never too small
+  inv_f = (float)inv;
+  // plane x0 is the near one when the ray travels towards +axis
+  c0 = inv > 0 ? cn : cf;
+  c1 = inv > 0 ? cf : cn;
+}
+
+DEV RaySetup make_setup(const DevScene &S, const Ray &r) {
+  RaySetup s;
+  const double m = fmax(fmax(fabs(r.d.x), fabs(r.d.y)), fabs(r.d.z)); // fmax drops NaNs; an all-NaN direction gives NaN
+  const long long e = (__double_as_longlong(m) >> 52) & 0x7ff;
+  // 2^(1023 - e) for normal m; zero / denormal / inf / NaN directions keep sc = 1 and fall into the clamps above
+  const bool ok = e >= 1 && e <= 2045;
+  const double sc = ok ? __longlong_as_double((2046LL - e) << 52) : 1.0; // 2^(1023 - e)
+  s.tsc = ok ? __longlong_as_double(e << 52) : 1.0;                      // 2^(e - 1023)
+  setup_axis(r.o.x, r.d.x * sc, S.bound[0], s.ix, s.c0x, s.c1x);
+  setup_axis(r.o.y, r.d.y * sc, S.bound[1], s.iy, s.c0y, s.c1y);
+  setup_axis(r.o.z, r.d.z * sc, S.bound[2], s.iz, s.c0z, s.c1z);
+  return s;
+}
+
+// Conservative entry / exit parameters of one box for the interval [lo, hi] (already rounded outward to fp32).
+DEV void slab32(float x0, float x1, float y0, float y1, float z0, float z1, const RaySetup &s, float lo, float hi, float &tn, float &tf) {
+  const float ax = __fmaf_rn(x0, s.ix, -s.c0x), bx = __fmaf_rn(x1, s.ix, -s.c1x);
+  const float ay = __fmaf_rn(y0, s.iy, -s.c0y), by = __fmaf_rn(y1, s.iy, -s.c1y);
+  const float az = __fmaf_rn(z0, s.iz, -s.c0z), bz = __fmaf_rn(z1, s.iz, -s.c1z);
+  // fminf / fmaxf drop NaNs (inf * 0 on an infinite plane): such an axis does not constrain the interval
+  const float n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), lo));
+  const float f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), hi));
+  const float K = 4.76837158203125e-7f; // 2^-21: the FFMA's own rounding, relative
+  tn = __fmaf_rn(-K, fabsf(n), n);
+  tf = __fmaf_rn(K, fabsf(f), f);
 }
 
 DEV void leaf_test(const DevScene &S, int32_t ref, const Ray &r, double lo, double hi, const Stream &st, int bounce, Best &best) {
@@ -51,6 +107,23 @@ DEV void leaf_test(const DevScene &S, int32_t ref, const Ray &r, double lo, doub
   }
 }
 
+// One inner node: test both children, return the nearer accepted child (or B200_DONE) and push the other.
+DEV int32_t node_step(const DevScene &S, int32_t cur, const RaySetup &rs, float lo32, float hi32, int32_t *stack, int &sp) {
+  const float4 *q = reinterpret_cast<const float4 *>(S.bvh + cur);
+  const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+  const int2 ch = __ldg(reinterpret_cast<const int2 *>(q + 3));
+  float ln, lf, rn, rf;
+  slab32(a.x, a.y, a.z, a.w, b.x, b.y, rs, lo32, hi32, ln, lf);
+  slab32(b.z, b.w, c.x, c.y, c.z, c.w, rs, lo32, hi32, rn, rf);
+  const bool hl = ln <= lf, hr = rn <= rf;
+  if (hl && hr) {
+    const bool left_first = ln <= rn;
+    if (sp < B200_STACK) stack[sp++] = left_first ? ch.y : ch.x;
+    return left_first ? ch.x : ch.y;
+  }
+  return hl ? ch.x : (hr ? ch.y : B200_DONE);
+}
+
 // world.hit(r, interval(lo, hi), rec) -> (entry, t); entry < 0 on a miss.
 DEV Best trace_closest(const DevScene &S, const Ray &r, double lo, double hi, const Stream &st, int bounce) {
   Best best;
@@ -58,44 +131,21 @@ DEV Best trace_closest(const DevScene &S, const Ray &r, double lo, double hi, co
   best.entry = -1;
   best.order = 0;
   if (S.bvh_root == B200_EMPTY_ROOT) return best;
-  if (S.bvh_root < 0) {
-    leaf_test(S, S.bvh_root, r, lo, hi, st, bounce, best);
-    return best;
-  }
-  const V inv = v3(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
+  const RaySetup rs = make_setup(S, r);
+  const float lo32 = __double2float_rd(lo * rs.tsc);
+  float hi32 = __double2float_ru(hi * rs.tsc);
   int32_t stack[B200_STACK];
   int sp = 0;
   int32_t cur = S.bvh_root;
   for (;;) {
-    const BvhNode *nd = S.bvh + cur;
-    double ln, lf, rn, rf;
-    const double far_limit = best.entry < 0 ? hi : best.t;
-    slab2(nd->lbox, r.o, inv, lo, far_limit, ln, lf);
-    slab2(nd->rbox, r.o, inv, lo, far_limit, rn, rf);
-    const int2 ch = __ldg(reinterpret_cast<const int2 *>(&nd->left));
-    const bool hl = ln <= lf, hr = rn <= rf;
-    int32_t next = B200_EMPTY_ROOT;
-    if (hl && hr) {
-      const bool left_first = ln <= rn;
-      next = left_first ? ch.x : ch.y;
-      const int32_t other = left_first ? ch.y : ch.x;
-      if (sp < B200_STACK) stack[sp++] = other;
-    } else if (hl) {
-      next = ch.x;
-    } else if (hr) {
-      next = ch.y;
+    while (cur >= 0) { // inner nodes
+      cur = node_step(S, cur, rs, lo32, hi32, stack, sp);
+      if (cur == B200_DONE && sp > 0) cur = stack[--sp];
     }
-    // descend; leaves are tested as they are reached
-    for (;;) {
-      if (next == B200_EMPTY_ROOT) {
-        if (sp == 0) return best;
-        next = stack[--sp];
-      }
-      if (next >= 0) break;
-      leaf_test(S, next, r, lo, hi, st, bounce, best);
-      next = B200_EMPTY_ROOT;
-    }
-    cur = next;
+    if (cur == B200_DONE) return best;
+    leaf_test(S, cur, r, lo, hi, st, bounce, best);
+    if (best.entry >= 0) hi32 = __double2float_ru(best.t * rs.tsc);
+    cur = sp > 0 ? stack[--sp] : B200_DONE;
   }
 }
 

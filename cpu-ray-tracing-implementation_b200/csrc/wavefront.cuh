@@ -23,7 +23,7 @@ namespace b200 {
 
 struct WaveCtl {
   unsigned long long next_sample, total_samples, rays, nan_samples, waves, extend_rays_dummy;
-  uint32_t n_cur, n_next, capacity, pad;
+  uint32_t n_cur, n_next, capacity, fetch; // fetch: next unclaimed ray of the persistent extend kernel
   uint32_t q_count[8];
 };
 
@@ -35,7 +35,7 @@ struct PathBuf { // one pool: 13 columns of `capacity` elements
 struct WaveParams {
   uint64_t seed;
   uint32_t npix, width;
-  int32_t spp_begin, max_depth, kill_zero, pad;
+  int32_t spp_begin, max_depth, kill_zero, refill; // refill: idle lanes per warp that trigger a fetch in k_extend_persistent
 };
 
 DEV Ray load_ray(const PathBuf &b, uint32_t i) { return Ray{v3(b.ox[i], b.oy[i], b.oz[i]), v3(b.dx[i], b.dy[i], b.dz[i]), b.tm[i]}; }
@@ -67,6 +67,7 @@ __global__ void k_ctl_init(WaveCtl *c, unsigned long long total, uint32_t capaci
   c->n_cur = 0;
   c->n_next = 0;
   c->capacity = capacity;
+  c->fetch = 0;
   for (int k = 0; k < 8; k++) c->q_count[k] = 0;
 }
 DEV uint32_t wave_refill(const WaveCtl *c) {
@@ -77,6 +78,7 @@ __global__ void k_ctl_generated(WaveCtl *c) {
   const uint32_t n = wave_refill(c);
   c->n_cur += n;
   c->next_sample += n;
+  c->fetch = 0;
 }
 __global__ void k_ctl_swap(WaveCtl *c) {
   unsigned long long r = 0;
@@ -164,6 +166,92 @@ __global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, PathBuf 
       }
     }
     classify(c, Q, i, which);
+  }
+}
+
+
+// The compacted-BVH extend as a persistent kernel (one CTA set sized to the SM count, no grid-stride loop):
+// every lane owns one ray; a warp whose idle lanes reach `wp.refill` claims that many new rays with ONE atomic and
+// continues, so lanes do not wait for the longest traversal of a fixed 32-ray batch (incoherent bounce rays differ
+// by an order of magnitude in node visits).  Inner structure: "while nodes / then one leaf" so that the binary32 box
+// filter and the binary64 leaf tests each run with as many lanes as possible.
+__global__ void __launch_bounds__(128, 4) k_extend_persistent(WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, Queues Q, WaveParams wp) {
+  const uint32_t n = c->n_cur;
+  const int lane = threadIdx.x & 31;
+  const unsigned FULL = 0xffffffffu;
+  const int refill = wp.refill, keep = 33 - wp.refill; // leave the traversal loop when fewer than `keep` lanes still run
+  bool active = false, pending = false, exhausted = false;
+  uint32_t idx = 0;
+  Ray r;
+  RaySetup rs;
+  Best best;
+  Stream st;
+  int bounce = 0, sp = 0;
+  float lo32 = 0, hi32 = 0;
+  int32_t node = B200_DONE;
+  int32_t stack[B200_STACK];
+  for (;;) {
+    __syncwarp();
+    if (__any_sync(FULL, pending)) { // retire finished rays: hit reference + index into the queue of what they hit
+      int which = -1;
+      if (pending) {
+        HitRef h;
+        h.t = best.entry < 0 ? 0.0 : best.t;
+        h.entry = best.entry;
+        hits[idx] = h;
+        which = best.entry < 0 ? B200_Q_MISS : S.materials[entry_material(S, S.entries[best.entry])].kind;
+        pending = false;
+      }
+      classify(c, Q, idx, which);
+    }
+    const unsigned idle = __ballot_sync(FULL, !active);
+    if (!exhausted && __popc(idle) >= refill) {
+      const uint32_t want = (uint32_t)__popc(idle);
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(&c->fetch, want);
+      base = __shfl_sync(FULL, base, 0);
+      if (!active) {
+        const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+        if (i < n) {
+          const uint32_t pixel = cur.pixel[i];
+          if (pixel != B200_DEAD) {
+            idx = i;
+            r = load_ray(cur, i);
+            st = Stream{wp.seed, pixel, cur.sample[i]};
+            bounce = (int)cur.bounce[i];
+            rs = make_setup(S, r);
+            lo32 = __double2float_rd(0.001 * rs.tsc);
+            hi32 = __int_as_float(0x7f800000);
+            best.t = B200_INF, best.entry = -1, best.order = 0;
+            sp = 0;
+            node = S.bvh_root;
+            active = true;
+          }
+        }
+      }
+      exhausted = base + want >= n;
+    }
+    if (!__any_sync(FULL, active)) {
+      if (exhausted) break;
+      continue;
+    }
+    while (active) {
+      while (node >= 0) {
+        node = node_step(S, node, rs, lo32, hi32, stack, sp);
+        if (node == B200_DONE && sp > 0) node = stack[--sp];
+      }
+      if (node != B200_DONE) {
+        leaf_test(S, node, r, 0.001, B200_INF, st, bounce, best);
+        if (best.entry >= 0) hi32 = __double2float_ru(best.t * rs.tsc);
+        node = sp > 0 ? stack[--sp] : B200_DONE;
+      }
+      if (node == B200_DONE) {
+        active = false;
+        pending = true;
+      } else if (!exhausted && __popc(__activemask()) < keep) {
+        break;
+      }
+    }
   }
 }
 

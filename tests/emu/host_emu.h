@@ -25,4 +25,29 @@ inline double __longlong_as_double(long long v) {
   std::memcpy(&d, &v, 8);
   return d;
 }
+inline long long __double_as_longlong(double d) {
+  long long v;
+  std::memcpy(&v, &d, 8);
+  return v;
+}
 using std::isnan;
+struct alignas(16) float4 {
+  float x, y, z, w;
+};
+inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
+inline float __int_as_float(int v) {
+  float f;
+  std::memcpy(&f, &v, 4);
+  return f;
+}
+inline float __double2float_rd(double x) {
+  float f = (float)x;
+  if ((double)f > x) f = std::nextafterf(f, -INFINITY);
+  return f;
+}
+inline float __double2float_ru(double x) {
+  float f = (float)x;
+  if ((double)f < x) f = std::nextafterf(f, INFINITY);
+  return f;
+}
+// fabsf / fmaxf / fminf: the C library's global-namespace functions

@@ -1,0 +1,79 @@
+"""CPU execution of the DEVICE FUNCTIONS of csrc/ (tests/emu: the same traverse / intersect / shading / camera source compiled
+with g++ behind stand-ins for the CUDA built-ins) against the reference's golden records and the oracle.  No kernel runs here;
+this pins the host logic (flattener, BVH builder, fp32 conservative box filter, tie-break by reference order) without a GPU."""
+import numpy as np
+import pytest
+from conftest import ALL_SCENES, VOLUME_SCENES, golden, same
+
+import emu
+
+
+@pytest.fixture(scope="module")
+def emu_lib():
+    emu.build()
+    return emu
+
+
+@pytest.mark.parametrize("leaf", [1, 2, 4])
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_emu_hits_vs_reference_golden(emu_lib, name, leaf):
+    g = golden(name)
+    es = emu_lib.EmuScene(g.scene, leaf_size=leaf)
+    out = es.trace(g["trace_rays"], seed=99)
+    keep = np.ones(len(out["prim"]), bool)
+    if name in VOLUME_SCENES:
+        vol = np.array(sorted(g.volume_prims()))
+        keep = ~np.isin(out["prim"], vol) & ~np.isin(g["trace_prim"], vol)
+    for k in ("prim", "front", "t", "p", "normal", "uv"):
+        ok = same(out[k][keep], g["trace_" + k][keep])
+        assert ok.all(), f"{name}: {k} differs on {(~ok).sum()} of {keep.sum()} rays"
+
+
+@pytest.mark.parametrize("name", ["cornell", "rtow", "fox", "rtnw"])
+def test_emu_mirror_equals_fast(emu_lib, name):
+    g = golden(name)
+    es = emu_lib.EmuScene(g.scene)
+    a, b = es.trace(g["trace_rays"], seed=5), es.trace(g["trace_rays"], seed=5, mirror=True)
+    for k in ("prim", "t", "front"):
+        assert same(a[k], b[k]).all(), k
+
+
+def test_emu_degenerate_rays_are_conservative(emu_lib, build_oracle):
+    """Axis-parallel, zero-component, huge, tiny and NaN rays: the fp32 box filter must never lose a hit the oracle finds."""
+    g = golden("rtow")
+    es = emu_lib.EmuScene(g.scene)
+    rng = np.random.RandomState(7)
+    n = 4000
+    rays = np.zeros((n, 7))
+    rays[:, 0:3] = rng.uniform(-12, 12, size=(n, 3)) * [1, 0.2, 1] + [0, 1.0, 0]
+    d = rng.normal(size=(n, 3))
+    d[rng.rand(n) < 0.3, 0] = 0.0
+    d[rng.rand(n) < 0.3, 2] = 0.0
+    d[rng.rand(n) < 0.1, 1] = 0.0
+    scale = 10.0 ** rng.uniform(-35, 35, size=(n, 1))
+    scale[rng.rand(n) < 0.5] = 1.0
+    rays[:, 3:6] = d * scale
+    rays[::97, 3] = np.nan
+    rays[5::101, 0] = 1e9
+    out = es.trace(rays, seed=3)
+    ref = build_oracle.trace(g.scene, rays, seed=3)
+    assert (out["prim"] == ref["prim"]).all()
+    assert same(out["t"], ref["t"]).all()
+
+
+@pytest.mark.parametrize("name", ["cornell", "rtow", "three_ball_lens", "skybox_fisheye"])
+def test_emu_camera_rays(emu_lib, name, build_oracle):
+    g = golden(name)
+    a = emu_lib.generate_rays(g.cam_small, 11, 0, 2)
+    b = build_oracle.generate_rays(g.cam_small, 11, 0, 2)
+    assert same(a, b).all()
+
+
+@pytest.mark.parametrize("name", ["cornell", "rtow", "cornell_volume", "light_earth"])
+def test_emu_render_equals_oracle(emu_lib, name, build_oracle):
+    g = golden(name)
+    a = emu_lib.EmuScene(g.scene).render(g.cam_small, 21, 0, 2)
+    b = build_oracle.render(g.scene, g.cam_small, 21, 0, 2, threads=0)
+    close = np.abs(a["sum"] - b["sum"]) <= 1e-9 * np.maximum(np.abs(b["sum"]), 1e-3)  # sincos / fused libm calls may differ in the last place
+    assert close.mean() > 0.995, close.mean()
+    assert abs(a["rays"] - b["stats"]["rays"]) <= 0.002 * b["stats"]["rays"] + 2
