@@ -60,6 +60,7 @@ struct b200rt_ctx {
   int kill_zero = 1;
   int bvh_leaf = 2;
   int refill_lanes = 32;
+  int extend_blocks = 4;
   // scene
   bool have_scene = false, have_camera = false;
   DevMem scene_mem;
@@ -210,6 +211,7 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     c->bvh_leaf = (int)value; // takes effect at the next b200rt_upload_scene
     return B200RT_OK;
   case B200RT_OPT_SMEM_NODES: return B200RT_OK; // reserved
+  case B200RT_OPT_EXTEND_BLOCKS: c->extend_blocks = (int)value; return B200RT_OK;
   case B200RT_OPT_REFILL_LANES:
     if (!(value >= 1 && value <= 32)) return fail(B200RT_ERR_INVALID, "refill lanes must be in [1, 32]");
     c->refill_lanes = (int)value;
@@ -442,12 +444,8 @@ int ensure_wave(b200rt_ctx *c, uint32_t capacity, bool mirror) {
   c->wave_capacity = 0;
   auto col = [&](void **p, size_t elem) { return c->wave_mem.alloc(p, (size_t)capacity * elem); };
   for (int b = 0; b < 2; b++) {
-    PathBuf &P = c->pool[b];
-    double **dcols[10] = {&P.ox, &P.oy, &P.oz, &P.dx, &P.dy, &P.dz, &P.tm, &P.tx, &P.ty, &P.tz};
-    for (auto dc : dcols) CU(col((void **)dc, sizeof(double)));
-    CU(col((void **)&P.pixel, 4));
-    CU(col((void **)&P.sample, 4));
-    CU(col((void **)&P.bounce, 4));
+    CU(col((void **)&c->pool[b].base, B200_PATH_QUADS * sizeof(double2)));
+    c->pool[b].capacity = capacity;
   }
   CU(col((void **)&c->hits, sizeof(HitRef)));
   c->recs = nullptr;
@@ -504,6 +502,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   wp.max_depth = c->cam.max_depth;
   wp.kill_zero = c->kill_zero;
   wp.refill = c->refill_lanes;
+  for (int k = 0; k < 3; k++) wp.bound[k] = c->S.bound[k];
   const DevCamera cam = make_camera(c->cam);
   const int g_gen = grid_for(c, capacity, 256, 8), g_ext = grid_for(c, capacity, 128, 16);
 
@@ -526,14 +525,20 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     if (mirror)
       k_extend<true><<<g_ext, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->recs, c->queues, wp);
     else
-      k_extend_persistent<<<c->sm_count * 4, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->queues, wp);
+      switch (c->extend_blocks) {
+      case 5: k_extend_persistent<5><<<c->sm_count * 5, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
+      case 6: k_extend_persistent<6><<<c->sm_count * 6, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
+      case 8: k_extend_persistent<8><<<c->sm_count * 8, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
+      default: k_extend_persistent<4><<<c->sm_count * 4, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
+      }
+    if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(c->ctl, c->hits, c->queues);
     if (stats) CU(cudaEventRecord(ext_events.back(), s));
     if (mirror)
       launch_shades<true>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
     else
       launch_shades<false>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
     k_ctl_swap<<<1, 1, 0, s>>>(c->ctl);
-    launches += 4 + B200_NQUEUES;
+    launches += (mirror ? 4 : 5) + B200_NQUEUES;
     wave++;
     if (wave >= next_check) {
       CU(cudaMemcpyAsync(c->h_ctl, c->ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, s));

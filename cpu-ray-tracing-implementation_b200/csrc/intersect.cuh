@@ -227,7 +227,13 @@ DEV bool entry_t(const DevScene &S, const Entry &e, const Ray &rw, double lo, do
 }
 
 // ---------------------------------------------------------------- (leaf, t) -> hit_record
-DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, Rec &rec) {
+// uv_mode: 1 = always fill rec.u, rec.v (b200rt_trace); 2 = only when the material's texture reads them (picture_texture is
+// the only texture::sample that looks at u, v: src/texture.h:12-119), which spares the shading kernels acos + atan2 per sphere hit.
+#define B200_UV_ALWAYS 1
+#define B200_UV_IF_USED 2
+DEV bool material_reads_uv(const DevScene &S, int mat) { return S.textures[S.materials[mat].tex].kind == B200RT_TEX_PICTURE; }
+
+DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, Rec &rec, int uv_mode = B200_UV_ALWAYS) {
   const int chain = entry_chain(e);
   const Ray r = chain_apply(S, chain, rw);
   rec.t = t;
@@ -240,19 +246,21 @@ DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, 
   case E_SPHERE_MOVING: {
     const double *q = S.spheres + (size_t)e.row * B200RT_SPHERE_STRIDE;
     const V outward = (rec.p - v3(q[0], q[1], q[2])) / q[3]; // center_, also for moving spheres: src/sphere.h:69
-    get_sphere_uv(outward, rec.u, rec.v);
-    set_face_normal(rec, r, outward);
     rec.mat = S.sphere_mat[e.row];
+    if (uv_mode == B200_UV_ALWAYS || material_reads_uv(S, rec.mat)) get_sphere_uv(outward, rec.u, rec.v);
+    set_face_normal(rec, r, outward);
     break;
   }
   case E_QUAD: {
     const double *q = S.quads + (size_t)e.row * B200RT_QUAD_STRIDE;
     const V p = rec.p - v3(q[0], q[1], q[2]);
     const V w = v3(q[12], q[13], q[14]);
-    rec.u = dot(w, cross(p, v3(q[6], q[7], q[8])));
-    rec.v = dot(w, cross(v3(q[3], q[4], q[5]), p));
-    set_face_normal(rec, r, v3(q[9], q[10], q[11]));
     rec.mat = S.quad_mat[e.row];
+    if (uv_mode == B200_UV_ALWAYS || material_reads_uv(S, rec.mat)) {
+      rec.u = dot(w, cross(p, v3(q[6], q[7], q[8])));
+      rec.v = dot(w, cross(v3(q[3], q[4], q[5]), p));
+    }
+    set_face_normal(rec, r, v3(q[9], q[10], q[11]));
     break;
   }
   case E_TRI: {

@@ -94,9 +94,10 @@ struct DevScene {
 };
 
 // What extend leaves behind for shade: enough to rebuild the full hit_record deterministically.
-struct HitRef {
+struct __align__(16) HitRef {
   double t;
-  int32_t entry; // index into entries, -1 = miss
+  int32_t entry; // index into entries, -1 = miss, -2 = dead slot (no ray was traced)
+  int32_t queue; // which shade queue the path goes to: b200rt_material_kind of the hit, B200_Q_MISS, or -1 for none
 };
 
 struct Rec { // src/hittable.h:7-30

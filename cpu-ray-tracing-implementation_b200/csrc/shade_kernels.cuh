@@ -15,20 +15,26 @@ DEV void accumulate(double *accum, uint32_t pixel, V c) { // image_[i*W+j] += sa
 template <int KIND, bool MIRROR>
 __global__ void __launch_bounds__(128) k_shade(WaveCtl *c, DevScene S, PathBuf cur, PathBuf nxt, const HitRef *hits, const Rec *recs,
                                                 const uint32_t *queue, double *accum, WaveParams wp) {
+  // survivors are appended to the other pool with ONE global atomic per CTA iteration (same-address atomics are the
+  // scarce resource of this kernel family: see k_classify); double-buffered by iteration parity
+  __shared__ uint32_t s_cnt[2][4], s_base[2];
   const uint32_t n = c->q_count[KIND];
-  for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x) {
-    const uint32_t j = base + (threadIdx.x & 31);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int par = 0;
+  for (uint32_t bbase = blockIdx.x * 128; bbase < n; bbase += gridDim.x * 128, par ^= 1) {
+    const uint32_t j = bbase + threadIdx.x;
     bool survives = false;
     Ray out_ray;
     V T;
     uint32_t pixel = 0, sample = 0, bounce = 0;
     if (j < n) {
       const uint32_t i = queue[j];
-      const Ray r = load_ray(cur, i);
-      T = v3(cur.tx[i], cur.ty[i], cur.tz[i]);
-      pixel = cur.pixel[i];
-      sample = cur.sample[i];
-      bounce = cur.bounce[i];
+      const PathHead ph = load_head(cur, i);
+      const Ray r = ph.r;
+      T = load_throughput(cur, i);
+      pixel = ph.pixel;
+      sample = ph.sample;
+      bounce = ph.bounce;
       if (KIND == B200_Q_MISS) {
         accumulate(accum, pixel, T * miss_color(S, r));
       } else {
@@ -37,10 +43,10 @@ __global__ void __launch_bounds__(128) k_shade(WaveCtl *c, DevScene S, PathBuf c
           rec = recs[i];
         } else {
           const HitRef h = hits[i];
-          finish_hit(S, S.entries[h.entry], r, h.t, rec);
+          finish_hit(S, S.entries[h.entry], r, h.t, rec, B200_UV_IF_USED);
         }
         const Stream st{wp.seed, pixel, sample};
-        const Scatter sc = shade_hit(S, rec, r, st, (int)bounce);
+        const Scatter sc = shade_hit<KIND>(S, rec, r, st, (int)bounce);
         if (sc.ends) {
           accumulate(accum, pixel, T * sc.value);
         } else {
@@ -53,13 +59,18 @@ __global__ void __launch_bounds__(128) k_shade(WaveCtl *c, DevScene S, PathBuf c
         }
       }
     }
-    const uint32_t pos = warp_append(&c->n_next, survives);
+    const unsigned smask = __ballot_sync(0xffffffffu, survives);
+    if (lane == 0) s_cnt[par][warp] = (uint32_t)__popc(smask);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t tot = s_cnt[par][0] + s_cnt[par][1] + s_cnt[par][2] + s_cnt[par][3];
+      s_base[par] = tot ? atomicAdd(&c->n_next, tot) : 0;
+    }
+    __syncthreads();
+    uint32_t pos = s_base[par] + (uint32_t)__popc(smask & ((1u << lane) - 1u));
+    for (int w = 0; w < warp; w++) pos += s_cnt[par][w];
     if (survives) {
-      store_ray(nxt, pos, out_ray);
-      nxt.tx[pos] = T.x, nxt.ty[pos] = T.y, nxt.tz[pos] = T.z;
-      nxt.pixel[pos] = pixel;
-      nxt.sample[pos] = sample;
-      nxt.bounce[pos] = bounce;
+      store_path(nxt, pos, out_ray, T, pixel, sample, bounce, make_setup(wp.bound, out_ray));
     }
   }
 }

@@ -110,9 +110,11 @@ struct Scatter {
 };
 
 // One level of ray_color below the hit test (src/camera.h:202-240).  `b` = scatters so far on this path.
-DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const Stream &st, int b) {
+// KIND >= 0: the caller knows the material kind at compile time (material-sorted queues), so only that branch is compiled in.
+template <int KIND = -1> DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const Stream &st, int b) {
   Scatter out;
-  const b200rt_material m = S.materials[rec.mat];
+  b200rt_material m = S.materials[rec.mat];
+  if (KIND >= 0) m.kind = KIND;
   if (m.kind == B200RT_MAT_DIFFUSE_LIGHT) { // src/material.h:211-215; scatter() is the base's false (:43)
     out.ends = true;
     out.value = rec.front_face ? tex_sample(S, m.tex, rec.u, rec.v, rec.p) : v3(0, 0, 0);

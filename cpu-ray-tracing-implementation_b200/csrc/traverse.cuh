@@ -61,17 +61,27 @@ DEV void setup_axis(double o, double d, double M, float &inv_f, float &c0, float
   c1 = inv > 0 ? cf : cn;
 }
 
-DEV RaySetup make_setup(const DevScene &S, const Ray &r) {
+// Largest biased exponent among the direction components, or 0 when it cannot be used as a scale (zero / denormal /
+// inf / NaN directions: scale 1, and setup_axis' clamps take over).
+DEV long long ray_exponent(const V &d) {
+  const long long ex = (__double_as_longlong(d.x) >> 52) & 0x7ff, ey = (__double_as_longlong(d.y) >> 52) & 0x7ff, ez = (__double_as_longlong(d.z) >> 52) & 0x7ff;
+  long long e = ex > ey ? ex : ey;
+  e = e > ez ? e : ez;
+  return (e >= 1 && e <= 2045) ? e : 0;
+}
+DEV double ray_tsc(const V &d) { // 2^(e - 1023)
+  const long long e = ray_exponent(d);
+  return e ? __longlong_as_double(e << 52) : 1.0;
+}
+
+DEV RaySetup make_setup(const double *bound, const Ray &r) {
   RaySetup s;
-  const double m = fmax(fmax(fabs(r.d.x), fabs(r.d.y)), fabs(r.d.z)); // fmax drops NaNs; an all-NaN direction gives NaN
-  const long long e = (__double_as_longlong(m) >> 52) & 0x7ff;
-  // 2^(1023 - e) for normal m; zero / denormal / inf / NaN directions keep sc = 1 and fall into the clamps above
-  const bool ok = e >= 1 && e <= 2045;
-  const double sc = ok ? __longlong_as_double((2046LL - e) << 52) : 1.0; // 2^(1023 - e)
-  s.tsc = ok ? __longlong_as_double(e << 52) : 1.0;                      // 2^(e - 1023)
-  setup_axis(r.o.x, r.d.x * sc, S.bound[0], s.ix, s.c0x, s.c1x);
-  setup_axis(r.o.y, r.d.y * sc, S.bound[1], s.iy, s.c0y, s.c1y);
-  setup_axis(r.o.z, r.d.z * sc, S.bound[2], s.iz, s.c0z, s.c1z);
+  const long long e = ray_exponent(r.d);
+  s.tsc = e ? __longlong_as_double(e << 52) : 1.0;
+  const double sc = e ? __longlong_as_double((2046LL - e) << 52) : 1.0; // 1 / tsc
+  setup_axis(r.o.x, r.d.x * sc, bound[0], s.ix, s.c0x, s.c1x);
+  setup_axis(r.o.y, r.d.y * sc, bound[1], s.iy, s.c0y, s.c1y);
+  setup_axis(r.o.z, r.d.z * sc, bound[2], s.iz, s.c0z, s.c1z);
   return s;
 }
 
@@ -131,7 +141,7 @@ DEV Best trace_closest(const DevScene &S, const Ray &r, double lo, double hi, co
   best.entry = -1;
   best.order = 0;
   if (S.bvh_root == B200_EMPTY_ROOT) return best;
-  const RaySetup rs = make_setup(S, r);
+  const RaySetup rs = make_setup(S.bound, r);
   const float lo32 = __double2float_rd(lo * rs.tsc);
   float hi32 = __double2float_ru(hi * rs.tsc);
   int32_t stack[B200_STACK];

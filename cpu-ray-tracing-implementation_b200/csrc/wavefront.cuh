@@ -27,22 +27,64 @@ struct WaveCtl {
   uint32_t q_count[8];
 };
 
-struct PathBuf { // one pool: 13 columns of `capacity` elements
-  double *ox, *oy, *oz, *dx, *dy, *dz, *tm, *tx, *ty, *tz;
-  uint32_t *pixel, *sample, *bounce;
+// Path state = eight 16-byte columns ("quads") of `capacity` elements each: every access is one 128-bit load or
+// store, a warp working on consecutive paths (extend batches, compacted appends of the shade kernels) moves 512
+// contiguous bytes per instruction, and the queue-ordered gathers of the shade kernels touch 6 sectors per path
+// instead of 13.  The fp32 box-filter constants (traverse.cuh) are computed by the PRODUCER of the ray (k_generate /
+// k_shade) and ride along in quads 4-6, so the extend kernel starts traversing straight away.
+//   q0 {o.x o.y}  q1 {o.z d.x}  q2 {d.y d.z}  q3 {time T.x}  q4 {ix iy iz c0x}  q5 {c1x c0y c1y c0z}
+//   q6 {c1z pixel sample bounce}  q7 {T.y T.z}
+#define B200_PATH_QUADS 8
+struct PathBuf {
+  double2 *base;
+  uint32_t capacity;
 };
+DEV const double2 *quad_ptr(const PathBuf &b, int q, uint32_t i) { return b.base + (size_t)q * b.capacity + i; }
 
 struct WaveParams {
   uint64_t seed;
   uint32_t npix, width;
   int32_t spp_begin, max_depth, kill_zero, refill; // refill: idle lanes per warp that trigger a fetch in k_extend_persistent
+  double bound[3]; // DevScene::bound, for the producers' make_setup
 };
 
-DEV Ray load_ray(const PathBuf &b, uint32_t i) { return Ray{v3(b.ox[i], b.oy[i], b.oz[i]), v3(b.dx[i], b.dy[i], b.dz[i]), b.tm[i]}; }
-DEV void store_ray(const PathBuf &b, uint32_t i, const Ray &r) {
-  b.ox[i] = r.o.x, b.oy[i] = r.o.y, b.oz[i] = r.o.z;
-  b.dx[i] = r.d.x, b.dy[i] = r.d.y, b.dz[i] = r.d.z;
-  b.tm[i] = r.tm;
+struct PathHead { // what every consumer needs
+  Ray r;
+  uint32_t pixel, sample, bounce;
+};
+DEV PathHead load_head(const PathBuf &b, uint32_t i) {
+  const double2 q0 = __ldg(quad_ptr(b, 0, i)), q1 = __ldg(quad_ptr(b, 1, i)), q2 = __ldg(quad_ptr(b, 2, i)), q3 = __ldg(quad_ptr(b, 3, i));
+  const int4 q6 = __ldg(reinterpret_cast<const int4 *>(quad_ptr(b, 6, i)));
+  PathHead h;
+  h.r = Ray{v3(q0.x, q0.y, q1.x), v3(q1.y, q2.x, q2.y), q3.x};
+  h.pixel = (uint32_t)q6.y, h.sample = (uint32_t)q6.z, h.bounce = (uint32_t)q6.w;
+  return h;
+}
+DEV V load_throughput(const PathBuf &b, uint32_t i) {
+  const double2 q3 = __ldg(quad_ptr(b, 3, i)), q7 = __ldg(quad_ptr(b, 7, i));
+  return v3(q3.y, q7.x, q7.y);
+}
+DEV RaySetup load_setup(const PathBuf &b, uint32_t i, const Ray &r) {
+  const float4 q4 = __ldg(reinterpret_cast<const float4 *>(quad_ptr(b, 4, i))), q5 = __ldg(reinterpret_cast<const float4 *>(quad_ptr(b, 5, i)));
+  const float4 q6 = __ldg(reinterpret_cast<const float4 *>(quad_ptr(b, 6, i)));
+  RaySetup s;
+  s.ix = q4.x, s.iy = q4.y, s.iz = q4.z, s.c0x = q4.w;
+  s.c1x = q5.x, s.c0y = q5.y, s.c1y = q5.z, s.c0z = q5.w;
+  s.c1z = q6.x;
+  s.tsc = ray_tsc(r.d);
+  return s;
+}
+DEV void store_path(const PathBuf &b, uint32_t i, const Ray &r, const V &T, uint32_t pixel, uint32_t sample, uint32_t bounce, const RaySetup &s) {
+  double2 *q = b.base + i;
+  const size_t n = b.capacity;
+  q[0] = make_double2(r.o.x, r.o.y);
+  q[n] = make_double2(r.o.z, r.d.x);
+  q[2 * n] = make_double2(r.d.y, r.d.z);
+  q[3 * n] = make_double2(r.tm, T.x);
+  *reinterpret_cast<float4 *>(q + 4 * n) = make_float4(s.ix, s.iy, s.iz, s.c0x);
+  *reinterpret_cast<float4 *>(q + 5 * n) = make_float4(s.c1x, s.c0y, s.c1y, s.c0z);
+  *reinterpret_cast<float4 *>(q + 6 * n) = make_float4(s.c1z, __uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(bounce));
+  q[7 * n] = make_double2(T.y, T.z);
 }
 
 // warp-aggregated append: one atomic per warp per queue; must be reached by all 32 lanes
@@ -101,11 +143,7 @@ __global__ void __launch_bounds__(256) k_generate(const WaveCtl *c, PathBuf cur,
     const Ray r = generate_ray(cam, st, (int)(pixel / wp.width), (int)(pixel % wp.width));
     const uint32_t slot = n_cur + idx;
     const bool bad = isnan(r.d.x) || isnan(r.d.y) || isnan(r.d.z); // fisheye outside the image circle: contributes exactly 0
-    store_ray(cur, slot, r);
-    cur.tx[slot] = 1.0, cur.ty[slot] = 1.0, cur.tz[slot] = 1.0;
-    cur.pixel[slot] = bad ? B200_DEAD : pixel;
-    cur.sample[slot] = sample;
-    cur.bounce[slot] = 0;
+    store_path(cur, slot, r, v3(1.0, 1.0, 1.0), bad ? B200_DEAD : pixel, sample, 0, make_setup(wp.bound, r));
     if (bad) atomicAdd(nan_samples, 1ull);
   }
 }
@@ -125,6 +163,12 @@ struct Queues {
   uint32_t *q[B200_NQUEUES];
 };
 
+DEV void store_hit(HitRef *hits, uint32_t i, double t, int32_t entry, int32_t queue) { // one 128-bit store
+  int4 w;
+  w.x = __double2loint(t), w.y = __double2hiint(t), w.z = entry, w.w = queue;
+  *reinterpret_cast<int4 *>(hits + i) = w;
+}
+
 DEV void classify(WaveCtl *c, const Queues &Q, uint32_t i, int which) {
 #pragma unroll
   for (int k = 0; k < B200_NQUEUES; k++) {
@@ -142,11 +186,11 @@ __global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, PathBuf 
     const uint32_t i = base + (threadIdx.x & 31);
     int which = -1;
     if (i < n) {
-      const uint32_t pixel = cur.pixel[i];
-      if (pixel != B200_DEAD) {
-        const Ray r = load_ray(cur, i);
-        const Stream st{wp.seed, pixel, cur.sample[i]};
-        const int bounce = (int)cur.bounce[i];
+      const PathHead ph = load_head(cur, i);
+      if (ph.pixel != B200_DEAD) {
+        const Ray r = ph.r;
+        const Stream st{wp.seed, ph.pixel, ph.sample};
+        const int bounce = (int)ph.bounce;
         HitRef h;
         if (MIRROR) {
           MirrorCtx cx{&S, st, bounce};
@@ -154,12 +198,14 @@ __global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, PathBuf 
           const bool ok = mirror_hit(cx, (int)S.root, r, 0.001, B200_INF, rec, 0);
           h.t = ok ? rec.t : 0.0;
           h.entry = ok ? 0 : -1;
+          h.queue = -1;
           if (ok) recs[i] = rec;
           which = ok ? S.materials[rec.mat].kind : B200_Q_MISS;
         } else {
           const Best b = trace_closest(S, r, 0.001, B200_INF, st, bounce);
           h.t = b.t;
           h.entry = b.entry;
+          h.queue = -1;
           which = b.entry < 0 ? B200_Q_MISS : S.materials[entry_material(S, S.entries[b.entry])].kind;
         }
         hits[i] = h;
@@ -170,17 +216,61 @@ __global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, PathBuf 
 }
 
 
-// The compacted-BVH extend as a persistent kernel (one CTA set sized to the SM count, no grid-stride loop):
-// every lane owns one ray; a warp whose idle lanes reach `wp.refill` claims that many new rays with ONE atomic and
-// continues, so lanes do not wait for the longest traversal of a fixed 32-ray batch (incoherent bounce rays differ
-// by an order of magnitude in node visits).  Inner structure: "while nodes / then one leaf" so that the binary32 box
-// filter and the binary64 leaf tests each run with as many lanes as possible.
-__global__ void __launch_bounds__(128, 4) k_extend_persistent(WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, Queues Q, WaveParams wp) {
+// ------------------------------------------------------------------------------------------------ persistent extend
+DEV void cp_async16(void *smem_dst, const void *gmem_src) {
+#ifndef B200_HOST_EMU
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src));
+#endif
+}
+DEV void cp_async_commit() {
+#ifndef B200_HOST_EMU
+  asm volatile("cp.async.commit_group;");
+#endif
+}
+DEV void cp_async_wait_all() {
+#ifndef B200_HOST_EMU
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+#endif
+}
+
+#define B200_EXT_QUADS 7 /* q0..q6: ray, time, filter constants, pixel/sample/bounce; the throughput (q7) stays in HBM */
+
+// The compacted-BVH extend as a persistent kernel: warps own batches of 32 consecutive rays (warp w takes batches
+// w, w + W, ...), and every batch is brought into shared memory by cp.async one batch AHEAD of its use, so the HBM
+// latency of the ray fetch overlaps the traversal of the previous batch.  Every lane owns one ray; when `wp.refill`
+// lanes of a warp have finished, they take the next rays from the staged batch (a few LDS.128, no global round
+// trip, no atomics) instead of idling until the slowest of 32 incoherent rays is done.  A finished lane stores its
+// {t, leaf} itself; sorting into material queues is a separate coalesced pass (k_classify).
+// Inner structure: "while nodes / then one leaf" so that the binary32 box filter and the binary64 leaf tests each
+// run with as many lanes as possible.
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp) {
+  __shared__ __align__(16) double2 stage_mem[4][2][B200_EXT_QUADS][32]; // warp x stage x quad x lane: 28 KB
   const uint32_t n = c->n_cur;
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const unsigned FULL = 0xffffffffu;
-  const int refill = wp.refill, keep = 33 - wp.refill; // leave the traversal loop when fewer than `keep` lanes still run
-  bool active = false, pending = false, exhausted = false;
+  const uint32_t n_warps = gridDim.x * 4, n_batches = (n + 31) / 32;
+  const int refill = wp.refill, keep = 33 - wp.refill;
+
+  auto prefetch = [&](int stg, uint32_t batch) { // one cp.async group per call, also when there is nothing to copy
+    const uint32_t i = batch * 32 + lane;
+    if (batch < n_batches && i < n) {
+#pragma unroll
+      for (int q = 0; q < B200_EXT_QUADS; q++) cp_async16(&stage_mem[wib][stg][q][lane], quad_ptr(cur, q, i));
+    }
+    cp_async_commit();
+  };
+
+  uint32_t batch = blockIdx.x * 4 + wib; // the batch staged in `stg`
+  int stg = 0;
+  prefetch(0, batch);
+  prefetch(1, batch + n_warps);
+  cp_async_wait_all();
+  __syncwarp();
+  uint32_t base = batch * 32, count = batch < n_batches ? min(32u, n - base) : 0u, taken = 0;
+
+  bool active = false;
   uint32_t idx = 0;
   Ray r;
   RaySetup rs;
@@ -192,47 +282,53 @@ __global__ void __launch_bounds__(128, 4) k_extend_persistent(WaveCtl *c, DevSce
   int32_t stack[B200_STACK];
   for (;;) {
     __syncwarp();
-    if (__any_sync(FULL, pending)) { // retire finished rays: hit reference + index into the queue of what they hit
-      int which = -1;
-      if (pending) {
-        HitRef h;
-        h.t = best.entry < 0 ? 0.0 : best.t;
-        h.entry = best.entry;
-        hits[idx] = h;
-        which = best.entry < 0 ? B200_Q_MISS : S.materials[entry_material(S, S.entries[best.entry])].kind;
-        pending = false;
-      }
-      classify(c, Q, idx, which);
-    }
-    const unsigned idle = __ballot_sync(FULL, !active);
-    if (!exhausted && __popc(idle) >= refill) {
-      const uint32_t want = (uint32_t)__popc(idle);
-      uint32_t base = 0;
-      if (lane == 0) base = atomicAdd(&c->fetch, want);
-      base = __shfl_sync(FULL, base, 0);
-      if (!active) {
-        const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
-        if (i < n) {
-          const uint32_t pixel = cur.pixel[i];
-          if (pixel != B200_DEAD) {
-            idx = i;
-            r = load_ray(cur, i);
-            st = Stream{wp.seed, pixel, cur.sample[i]};
-            bounce = (int)cur.bounce[i];
-            rs = make_setup(S, r);
+    unsigned idle = __ballot_sync(FULL, !active);
+    if (count > 0 && (__popc(idle) >= refill || idle == FULL)) {
+      while (idle != 0 && count > 0) {
+        if (taken == count) { // next staged batch; refill the stage just drained
+          const int drained = stg;
+          batch += n_warps;
+          stg ^= 1;
+          cp_async_wait_all();
+          __syncwarp();
+          base = batch * 32, count = batch < n_batches ? min(32u, n - base) : 0u, taken = 0;
+          prefetch(drained, batch + n_warps);
+          continue;
+        }
+        const uint32_t slot = taken + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+        const bool take = !active && slot < count;
+        if (take) {
+          const double2 *sm = &stage_mem[wib][stg][0][slot];
+          const double2 q0 = sm[0], q1 = sm[32], q2 = sm[64], q3 = sm[96];
+          const float4 q4 = *reinterpret_cast<const float4 *>(sm + 128), q5 = *reinterpret_cast<const float4 *>(sm + 160);
+          const float4 q6 = *reinterpret_cast<const float4 *>(sm + 192);
+          idx = base + slot;
+          const uint32_t pixel = __float_as_uint(q6.y);
+          if (pixel == B200_DEAD) { // a camera sample that produced no ray: nothing to trace, nothing to shade
+            store_hit(hits, idx, 0.0, -2, -1);
+          } else {
+            r = Ray{v3(q0.x, q0.y, q1.x), v3(q1.y, q2.x, q2.y), q3.x};
+            st = Stream{wp.seed, pixel, __float_as_uint(q6.z)};
+            bounce = (int)__float_as_uint(q6.w);
+            rs.ix = q4.x, rs.iy = q4.y, rs.iz = q4.z, rs.c0x = q4.w;
+            rs.c1x = q5.x, rs.c0y = q5.y, rs.c1y = q5.z, rs.c0z = q5.w;
+            rs.c1z = q6.x;
+            rs.tsc = ray_tsc(r.d);
             lo32 = __double2float_rd(0.001 * rs.tsc);
             hi32 = __int_as_float(0x7f800000);
             best.t = B200_INF, best.entry = -1, best.order = 0;
             sp = 0;
             node = S.bvh_root;
-            active = true;
+            active = node != B200_EMPTY_ROOT;
+            if (!active) store_hit(hits, idx, 0.0, -1, B200_Q_MISS);
           }
         }
+        taken += min((uint32_t)__popc(idle), count - taken);
+        idle = __ballot_sync(FULL, !active);
       }
-      exhausted = base + want >= n;
     }
     if (!__any_sync(FULL, active)) {
-      if (exhausted) break;
+      if (count == 0) break;
       continue;
     }
     while (active) {
@@ -246,12 +342,56 @@ __global__ void __launch_bounds__(128, 4) k_extend_persistent(WaveCtl *c, DevSce
         node = sp > 0 ? stack[--sp] : B200_DONE;
       }
       if (node == B200_DONE) {
+        if (best.entry < 0)
+          store_hit(hits, idx, 0.0, -1, B200_Q_MISS);
+        else
+          store_hit(hits, idx, best.t, best.entry, S.materials[entry_material(S, S.entries[best.entry])].kind);
         active = false;
-        pending = true;
-      } else if (!exhausted && __popc(__activemask()) < keep) {
+      } else if (count > 0 && __popc(__activemask()) < keep) {
         break;
       }
     }
+  }
+}
+
+// Sorts path indices into the queue of what they hit.  Separate from the traversal so that it is perfectly
+// coalesced.  Same-address global atomics run at about one per 2 ns on B200, so a warp-aggregated append (131 k
+// atomics per 4 Mi-path wave on 3-4 hot counters) costs more than the traversal of a short wave; here a CTA ranks a
+// chunk of 2048 paths in shared memory (ballot/popc per warp, one shared atomic per warp and queue) and claims its
+// range of every queue with ONE global atomic per queue per chunk.
+#define B200_CLASSIFY_K 8
+__global__ void __launch_bounds__(256) k_classify(WaveCtl *c, const HitRef *hits, Queues Q) {
+  __shared__ uint32_t s_count[B200_NQUEUES], s_base[B200_NQUEUES];
+  const uint32_t n = c->n_cur;
+  const int lane = threadIdx.x & 31;
+  const uint32_t chunk = 256 * B200_CLASSIFY_K;
+  for (uint32_t cbase = blockIdx.x * chunk; cbase < n; cbase += gridDim.x * chunk) {
+    if (threadIdx.x < B200_NQUEUES) s_count[threadIdx.x] = 0;
+    __syncthreads();
+    int which[B200_CLASSIFY_K];
+    uint32_t rank[B200_CLASSIFY_K];
+#pragma unroll
+    for (int k = 0; k < B200_CLASSIFY_K; k++) {
+      const uint32_t i = cbase + k * 256 + threadIdx.x;
+      which[k] = i < n ? __ldg(reinterpret_cast<const int4 *>(hits + i)).w : -1;
+      rank[k] = 0;
+#pragma unroll
+      for (int q = 0; q < B200_NQUEUES; q++) {
+        const unsigned m = __ballot_sync(0xffffffffu, which[k] == q);
+        if (m == 0) continue; // warp-uniform
+        uint32_t b = 0;
+        if (lane == __ffs(m) - 1) b = atomicAdd(&s_count[q], (uint32_t)__popc(m));
+        b = __shfl_sync(0xffffffffu, b, __ffs(m) - 1);
+        if (which[k] == q) rank[k] = b + (uint32_t)__popc(m & ((1u << lane) - 1u));
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < B200_NQUEUES) s_base[threadIdx.x] = s_count[threadIdx.x] ? atomicAdd(&c->q_count[threadIdx.x], s_count[threadIdx.x]) : 0;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < B200_CLASSIFY_K; k++)
+      if (which[k] >= 0) Q.q[which[k]][s_base[which[k]] + rank[k]] = cbase + k * 256 + threadIdx.x;
+    __syncthreads();
   }
 }
 

@@ -220,6 +220,7 @@ typedef enum b200rt_option {
   B200RT_OPT_KILL_ZERO_WEIGHT = 2, /* 1 (default): drop paths whose throughput is exactly 0 in all channels */
   B200RT_OPT_BVH_LEAF_SIZE = 3, /* max primitives per leaf of the compacted BVH  */
   B200RT_OPT_SMEM_NODES = 4,    /* top-of-tree nodes staged in shared memory (reserved) */
+  B200RT_OPT_EXTEND_BLOCKS = 6, /* tuning: resident CTAs per SM the persistent extend kernel is compiled for (4, 5, 6 or 8) */
   B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (default 32 = fixed 32-ray batches, measured fastest on RTOW) */
 } b200rt_option;
 

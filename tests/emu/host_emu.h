@@ -51,3 +51,10 @@ inline float __double2float_ru(double x) {
   return f;
 }
 // fabsf / fmaxf / fminf: the C library's global-namespace functions
+inline double2 make_double2(double x, double y) { return double2{x, y}; }
+inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
+inline float __uint_as_float(unsigned v) {
+  float f;
+  std::memcpy(&f, &v, 4);
+  return f;
+}
