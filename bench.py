@@ -27,7 +27,8 @@ sys.path.insert(0, ROOT)
 SCENE = "rtow"
 WORKLOAD = "RTOW final scene: 487 spheres (lambertian/metal/dielectric), lens DOF camera, 1200x675, 500 spp, max depth 50"
 METRIC, UNIT = "Mrays/s on RTOW final scene (1200x675, 500 spp, depth 50); Msamples/s alongside", "Mrays/s"
-EXTEND_BYTES_PER_RAY = 88  # k_extend: reads o,d,time (56 B) + pixel,sample,bounce (12 B); writes {t, entry} (16 B) + queue index (4 B)
+TRAFFIC_BYTES_PER_LAUNCH = 528.97e6  # profiles/r01_e_extend.txt: dram__bytes_read.sum 470.5 MB + dram__bytes_write.sum 58.5 MB (4 Mi-ray launch)
+EXTEND_BYTES_PER_RAY = 128  # k_extend_persistent: reads 7 of the 8 path quads (ray, time, box-filter constants, ids: 112 B), writes one HitRef (16 B)
 
 
 def peaks():
@@ -156,13 +157,12 @@ def run_ours(args):
     ctx.set_camera(cam)
     accum = torch.zeros(H * W * 3, dtype=torch.float64, device="cuda")
     stream = torch.cuda.current_stream()
-    lo, hi = rank * spp, (rank + 1) * spp  # disjoint global sample ranges
+    lo, hi = pkg.distributed.weak_sample_range(rank, world, spp)  # disjoint global sample ranges
 
     def step(want_stats=False):
         accum.zero_()
         st = ctx.render_device(args.seed, lo, hi, accum.data_ptr(), stream.cuda_stream, want_stats=want_stats)
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)  # NCCL over NVLink: the one exchange step of the path
+        pkg.distributed.reduce_sums(accum)  # NCCL over NVLink: the one exchange step of the path (no-op at N = 1)
         return st
 
     def fence():
@@ -228,10 +228,12 @@ def run_ours(args):
                 "config": {"workload": WORKLOAD, "spp_per_gpu": spp, "wave_paths": args.wave, "seed": args.seed, "rays_per_sample": rays / samples,
                            "l2": "wavefront state per wave (>= 500 MB) exceeds the 126 MB L2; the scene (~100 kB) is meant to stay cached",
                            "parallelism": f"sample-range split x{world}, NCCL reduce of the fp64 accumulators" if world > 1 else "single GPU"},
-                "roofline": {"bound": "hbm", "kernel": "k_extend<false>", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "peak_source": peak_src, "bytes_per_ray": EXTEND_BYTES_PER_RAY,
+                "roofline": {"bound": "hbm", "kernel": "k_extend_persistent", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": TRAFFIC_BYTES_PER_LAUNCH, "peak_source": peak_src, "bytes_per_ray": EXTEND_BYTES_PER_RAY,
                              "extend_share_of_step": st["extend_ms"] / st["gpu_ms"],
-                             "note": "latency/FP64-issue bound by design (binary64 reference-order arithmetic); see DESIGN.md and profiles/"},
+                             "algorithmic_bytes_per_launch": st["rays"] * EXTEND_BYTES_PER_RAY / max(1, st["waves"]), "launches": st["waves"],
+                             "note": "issue/latency bound, not HBM bound (fp32 box filter + binary64 reference-order leaf tests over an L1/L2-resident BVH); "
+                                     "traffic = dram read+write of one steady-state launch from profiles/ (ncu --set full); see DESIGN.md"},
                 "e2e": e2e, "gpu_launches": int(launches * args.steps), "clocks": clocks}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()

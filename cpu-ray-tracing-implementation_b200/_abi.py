@@ -124,6 +124,7 @@ class Stats(C.Structure):
         ("extend_ms", C.c_double),
         ("h2d_bytes", C.c_double),
         ("d2h_bytes", C.c_double),
+        ("waves", C.c_uint64),
     ]
 
     def as_dict(self):

@@ -531,8 +531,8 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
       case 8: k_extend_persistent<8><<<c->sm_count * 8, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
       default: k_extend_persistent<4><<<c->sm_count * 4, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
       }
-    if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(c->ctl, c->hits, c->queues);
     if (stats) CU(cudaEventRecord(ext_events.back(), s));
+    if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(c->ctl, c->hits, c->queues);
     if (mirror)
       launch_shades<true>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
     else
@@ -568,6 +568,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     stats->rays = c->h_ctl->rays;
     stats->nan_samples = c->h_ctl->nan_samples;
     stats->kernel_launches = launches;
+    stats->waves = wave;
   }
   return B200RT_OK;
 }

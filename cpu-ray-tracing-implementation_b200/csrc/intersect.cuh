@@ -89,9 +89,22 @@ DEV bool sphere_t(V center, double radius, const Ray &r, double lo, double hi, d
   const double disc = b * b - 4 * a * c;
   if (disc < 0) return false;
   const double sq = sqrt(disc);
-  double root = (-b - sq) / (2.0 * a);
-  if (!contains(lo, hi, root)) {
-    root = (-b + sq) / (2.0 * a);
+  const double den = 2.0 * a;
+  // root = num / den with den = 2 (d.d) > 0: a numerator beyond bound * den by more than 1e-9 relative is a certain
+  // "outside [lo, hi]" without dividing (same argument as in tri_row_t); everything else takes the reference's division.
+  const double K = 1e-9, l = lo * den, h = hi * den;
+  const bool usable = den > 1e-200 && den < 1e100;
+  double num = -b - sq;
+  bool out = usable && fabs(num) > 1e-200 && (num < l - K * fabs(l) || num > h + K * fabs(h));
+  double root = 0;
+  if (!out) {
+    root = num / den;
+    out = !contains(lo, hi, root);
+  }
+  if (out) {
+    num = -b + sq;
+    if (usable && fabs(num) > 1e-200 && (num < l - K * fabs(l) || num > h + K * fabs(h))) return false;
+    root = num / den;
     if (!contains(lo, hi, root)) return false;
   }
   t = root;
@@ -128,7 +141,15 @@ DEV bool quad_row_t(const DevScene &S, int row, const Ray &r, double lo, double 
   ld2(q + 10, n1, n2);
   ld2(q + 14, w2, D);
   const V unorm = v3(n0, n1, n2);
-  const double tt = (D - dot(unorm, r.o)) / dot(unorm, r.d);
+  const double qn = D - dot(unorm, r.o), qd = dot(unorm, r.d);
+  { // certain "t outside [lo, hi]" from numerator and denominator, without the division (see tri_row_t)
+    const double K = 1e-9, ad = fabs(qd), sn = qd < 0 ? -qn : qn;
+    if (ad > 1e-200 && ad < 1e100 && fabs(sn) > 1e-200) {
+      const double l = lo * ad, h = hi * ad;
+      if (sn < l - K * fabs(l) || sn > h + K * fabs(h)) return false;
+    }
+  }
+  const double tt = qn / qd;
   if (!contains(lo, hi, tt)) return false;
   ld2(q, c0, c1);
   ld2(q + 2, c2, u0);
@@ -159,7 +180,25 @@ DEV bool tri_row_t(const DevScene &S, int row, const Ray &r, double lo, double h
   const V e1 = p1 - p0, e2 = p2 - p0, sv = r.o - p0;
   const V s1 = cross(r.d, e2), s2 = cross(sv, e1);
   const double det = dot(s1, e1);
-  const double tt = dot(s2, e2) / det, b0 = dot(s1, sv) / det, b1 = dot(s2, r.d) / det;
+  const double nt = dot(s2, e2), n0 = dot(s1, sv), n1 = dot(s2, r.d);
+  // The reference divides all three numerators by det and then tests (src/triangle.h:8-15, 32-34).  Most candidates fail,
+  // and a CERTAIN failure can be read off the numerators: the quotient's sign is exact, and a numerator beyond its bound
+  // times det by more than 1e-9 relative (seven orders above the rounding of the products and of the division) is beyond it
+  // after the division too.  NaN / zero det make every comparison false and fall through to the reference's own arithmetic.
+  {
+    const double K = 1e-9, tiny = 1e-200, ad = fabs(det);
+    if (ad > tiny && ad < 1e100) { // quotients of numerators above `tiny` cannot underflow to a signed zero
+      const double st = det < 0 ? -nt : nt, s0 = det < 0 ? -n0 : n0, s1n = det < 0 ? -n1 : n1; // det's sign folded in
+      if (s0 < -tiny || s1n < -tiny) return false;      // b0 < 0 or b1 < 0
+      if (s0 + s1n > ad + K * ad) return false;          // b0 + b1 > 1 (both terms are >= -tiny here: no cancellation)
+      if (fabs(st) > tiny) {
+        const double l = lo * ad, h = hi * ad;           // +-inf bounds stay +-inf and never reject
+        if (st < l - K * fabs(l)) return false;          // t < lo
+        if (st > h + K * fabs(h)) return false;          // t > hi
+      }
+    }
+  }
+  const double tt = nt / det, b0 = n0 / det, b1 = n1 / det;
   if (tt < lo || tt > hi) return false;
   if (b0 < 0 || b1 < 0 || b0 + b1 > 1) return false;
   t = tt;

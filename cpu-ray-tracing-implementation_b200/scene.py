@@ -236,3 +236,140 @@ def sponza_standin_triangles(n_triangles=SPONZA_TRIANGLES, seed=7):
     hi = np.array([x1, y1, z1])
     tris = np.clip(tris, lo, hi)
     return np.ascontiguousarray(tris.reshape(-1, 9).astype(np.float32))
+
+
+def reference_like_bvh(boxes):
+    """Node table of the tree the reference's bvh_node constructor builds over `boxes` ((n, 6) rows x0,x1,y0,y1,z0,z1):
+    objects sorted by bounding-box x-min, ALWAYS axis 0 (src/bvh_node.h:20-31; a range of an array already sorted by the
+    same key stays sorted, so one stable sort fixes every level), median split (begin+end)/2 (:42-44), two objects ->
+    both leaves (:37-39), one object -> left_ == right_ (:34-36); box_ = aabb::enclose(left, right) through the interval
+    constructor, i.e. padded to 1e-4 where thinner (src/aabb.h:7-12, 35-40, 81-86).
+    -> (inner (m,) node_dtype rows whose a/b are: >= 0 inner-node index, < 0 ~object, root index)."""
+    n = len(boxes)
+    order = np.argsort(boxes[:, 0], kind="stable")
+    inner = []  # [a, b, box]
+
+    def pad(b):
+        b = b.copy()
+        for k in range(3):
+            if b[2 * k + 1] - b[2 * k] < 0.0001:
+                b[2 * k] -= 0.00005
+                b[2 * k + 1] += 0.00005
+        return b
+
+    def enclose(b1, b2):
+        out = np.empty(6)
+        out[0::2] = np.minimum(b1[0::2], b2[0::2])
+        out[1::2] = np.maximum(b1[1::2], b2[1::2])
+        return pad(out)
+
+    import sys
+
+    sys.setrecursionlimit(max(10000, sys.getrecursionlimit()))
+
+    def build(lo, hi):
+        me = len(inner)
+        inner.append(None)
+        cnt = hi - lo
+        if cnt == 1:
+            a = b = ~int(order[lo])
+            box = enclose(boxes[order[lo]], boxes[order[lo]])
+        elif cnt == 2:
+            a, b = ~int(order[lo]), ~int(order[lo + 1])
+            box = enclose(boxes[order[lo]], boxes[order[lo + 1]])
+        else:
+            mid = (lo + hi) // 2
+            a, ba = build(lo, mid)
+            b, bb = build(mid, hi)
+            box = enclose(ba, bb)
+        inner[me] = (a, b, box)
+        return me, box
+
+    root, _ = build(0, n)
+    return inner, root
+
+
+def sponza_standin_scene(n_triangles=SPONZA_TRIANGLES, seed=7):
+    """BASELINE.json configs[4] as the reference's sponza() builds it (src/main.cc:439-489) over the stand-in mesh:
+    every triangle lambertian white, quad light (0,1200,0) 500x500 emitting 10, one bvh_node over everything, the quad
+    passed as `light`.  Labelled "Sponza-standin": the real Sponza.bin is missing from the reference checkout."""
+    t32 = sponza_standin_triangles(n_triangles, seed)
+    t = t32.astype(np.float64)
+    p0, p1, p2 = t[:, 0:3], t[:, 3:6], t[:, 6:9]
+    e1, e2 = p1 - p0, p2 - p0
+    c = np.stack([e1[:, 1] * e2[:, 2] - e1[:, 2] * e2[:, 1], e1[:, 2] * e2[:, 0] - e1[:, 0] * e2[:, 2], e1[:, 0] * e2[:, 1] - e1[:, 1] * e2[:, 0]], axis=1)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        nrm = c / np.sqrt(c[:, 0] * c[:, 0] + c[:, 1] * c[:, 1] + c[:, 2] * c[:, 2])[:, None]  # unit_vector(cross(p1-p0, p2-p0)), src/triangle.h:24
+    s = Scene()
+    s.name = "sponza-standin"
+    s.tris = np.ascontiguousarray(np.concatenate([t, nrm], axis=1))
+    s.tri_mat = np.zeros(len(t), dtype="<i4")
+    # quad light: corner, u, v, unorm, w = n / dot(n, n), D = dot(unorm, corner), area (include/b200rt.h B200RT_QUAD_STRIDE)
+    corner, u, v = np.array([0.0, 1200.0, 0.0]), np.array([500.0, 0.0, 0.0]), np.array([0.0, 0.0, 500.0])
+    nq = np.array([u[1] * v[2] - u[2] * v[1], u[2] * v[0] - u[0] * v[2], u[0] * v[1] - u[1] * v[0]])
+    area = float(np.sqrt(nq[0] * nq[0] + nq[1] * nq[1] + nq[2] * nq[2]))
+    unorm = nq / area
+    w = nq / (nq[0] * nq[0] + nq[1] * nq[1] + nq[2] * nq[2])
+    q = np.zeros((1, abi.QUAD_STRIDE))
+    q[0, 0:3], q[0, 3:6], q[0, 6:9], q[0, 9:12], q[0, 12:15] = corner, u, v, unorm, w
+    q[0, 15] = unorm[0] * corner[0] + unorm[1] * corner[1] + unorm[2] * corner[2]
+    q[0, 16] = area
+    s.quads = q
+    s.quad_mat = np.array([1], dtype="<i4")
+    s.textures = np.zeros(2, dtype=abi.texture_dtype)
+    s.textures["kind"] = abi.TEX_SOLID
+    s.textures["c0"][0] = 1.0
+    s.textures["c0"][1] = 10.0
+    s.materials = np.zeros(2, dtype=abi.material_dtype)
+    s.materials["kind"] = [abi.MAT_LAMBERTIAN, abi.MAT_DIFFUSE_LIGHT]
+    s.materials["tex"] = [0, 1]
+    # object boxes: triangle = aabb(min, max) unpadded (src/triangle.h:42-48); quad = enclose of its two diagonals (src/quad.h:19-21)
+    nt = len(t)
+    boxes = np.empty((nt + 1, 6))
+    P = t.reshape(nt, 3, 3)
+    boxes[:nt, 0::2] = P.min(axis=1)
+    boxes[:nt, 1::2] = P.max(axis=1)
+    qb = np.stack([corner, corner + u, corner + v, corner + u + v])
+    qbox = np.empty(6)
+    qbox[0::2], qbox[1::2] = qb.min(axis=0), qb.max(axis=0)
+    for k in range(3):
+        if qbox[2 * k + 1] - qbox[2 * k] < 0.0001:
+            qbox[2 * k] -= 0.00005
+            qbox[2 * k + 1] += 0.00005
+    boxes[nt] = qbox
+    inner, root = reference_like_bvh(boxes)
+    m = len(inner)
+    nodes = np.zeros(m + nt + 1, dtype=abi.node_dtype)
+    # leaves first: node i (< nt) = triangle i, node nt = the quad; inner node k lives at nt + 1 + k
+    nodes["kind"][:nt] = abi.NODE_TRIANGLE
+    nodes["a"][:nt] = np.arange(nt)
+    nodes["kind"][nt] = abi.NODE_QUAD
+    nodes["a"][nt] = 0
+    ia = np.array([x[0] for x in inner], dtype=np.int64)
+    ib = np.array([x[1] for x in inner], dtype=np.int64)
+    nodes["kind"][nt + 1:] = abi.NODE_BVH
+    nodes["a"][nt + 1:] = np.where(ia >= 0, ia + nt + 1, ~ia)
+    nodes["b"][nt + 1:] = np.where(ib >= 0, ib + nt + 1, ~ib)
+    nodes["f"][nt + 1:] = np.array([x[2] for x in inner])
+    # primitive ids = order of first visit in the reference's left-to-right depth-first walk
+    ids = np.full(nt + 1, -1, dtype=np.int64)
+    nxt = 0
+    stack = [root]
+    while stack:
+        k = stack.pop()
+        if k < 0:
+            o = ~k
+            if ids[o] < 0:
+                ids[o] = nxt
+                nxt += 1
+            continue
+        stack.append(int(ib[k]))
+        stack.append(int(ia[k]))
+    nodes["c"][: nt + 1] = ids
+    s.nodes = nodes
+    s.root = nt + 1 + root
+    s.n_primitives = nt + 1
+    s.light_kind = abi.LIGHT_QUAD
+    s.light_index = 0
+    s.background_tex = -1
+    return s

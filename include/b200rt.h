@@ -236,6 +236,7 @@ typedef struct b200rt_stats {
   double extend_ms;       /* of which: traversal kernels                                 */
   double h2d_bytes;
   double d2h_bytes;
+  uint64_t waves;         /* wavefront iterations = launches of the extend kernel         */
 } b200rt_stats;
 
 typedef struct b200rt_ctx b200rt_ctx;
