@@ -250,7 +250,7 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step (default: the config's 500)")
-    ap.add_argument("--wave", type=int, default=1 << 22, help="paths resident per wave")
+    ap.add_argument("--wave", type=int, default=1 << 24, help="paths resident per wave")
     ap.add_argument("--seed", type=int, default=0x5EED)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--refill", type=int, default=0, help="tuning: idle lanes per warp that trigger a ray fetch in the persistent extend kernel")

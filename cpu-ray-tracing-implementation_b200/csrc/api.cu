@@ -56,11 +56,12 @@ struct b200rt_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // options
   int traversal = B200RT_TRAVERSAL_FAST;
-  uint32_t wave_paths = 1u << 22;
+  uint32_t wave_paths = 1u << 24;
   int kill_zero = 1;
-  int bvh_leaf = 2;
-  int refill_lanes = 32;
+  int bvh_leaf = 0;     // 0 = by scene size (profiles/r01_g_tune.txt): 1 primitive per leaf up to 8192 primitives, else 2
+  int refill_lanes = 0; // 0 = by BVH size: fixed 32-ray batches for cache-resident trees, refill at 16 idle lanes from 32 Ki nodes
   int extend_blocks = 4;
+  int speculative = 0;
   // scene
   bool have_scene = false, have_camera = false;
   DevMem scene_mem;
@@ -68,6 +69,7 @@ struct b200rt_ctx {
   b200rt_bvh_info bvh_info{};
   double scene_h2d_bytes = 0;
   int graph_depth = 0;
+  uint32_t kinds_present = 0; // bit k: some material of the scene has b200rt_material_kind k (queues of absent kinds stay empty)
   // camera
   b200rt_camera cam{};
   // wavefront pools
@@ -207,13 +209,14 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     return B200RT_OK;
   case B200RT_OPT_KILL_ZERO_WEIGHT: c->kill_zero = value != 0; return B200RT_OK;
   case B200RT_OPT_BVH_LEAF_SIZE:
-    if (!(value >= 1 && value <= 8)) return fail(B200RT_ERR_INVALID, "leaf size must be in [1, 8]");
+    if (!(value >= 0 && value <= 8)) return fail(B200RT_ERR_INVALID, "leaf size must be in [0, 8] (0 = automatic)");
     c->bvh_leaf = (int)value; // takes effect at the next b200rt_upload_scene
     return B200RT_OK;
   case B200RT_OPT_SMEM_NODES: return B200RT_OK; // reserved
   case B200RT_OPT_EXTEND_BLOCKS: c->extend_blocks = (int)value; return B200RT_OK;
+  case B200RT_OPT_SPECULATIVE_LEAF: c->speculative = value != 0; return B200RT_OK;
   case B200RT_OPT_REFILL_LANES:
-    if (!(value >= 1 && value <= 32)) return fail(B200RT_ERR_INVALID, "refill lanes must be in [1, 32]");
+    if (!(value >= 0 && value <= 32)) return fail(B200RT_ERR_INVALID, "refill lanes must be in [0, 32] (0 = automatic)");
     c->refill_lanes = (int)value;
     return B200RT_OK;
   }
@@ -250,7 +253,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
       if (mat < 0 || (uint32_t)mat >= d->n_materials)
         return fail(B200RT_ERR_UNSUPPORTED, "primitive %d has no material (the reference would dereference a null pointer)", e.prim);
     }
-    bvh = BvhBuilder(fs.boxes, c->bvh_leaf).run();
+    bvh = BvhBuilder(fs.boxes, c->bvh_leaf ? c->bvh_leaf : (fs.boxes.size() <= 8192 ? 1 : 2)).run();
     ordered.resize(fs.entries.size());
     for (size_t k = 0; k < ordered.size(); k++) ordered[k] = fs.entries[bvh.perm[k]];
   } catch (const std::exception &e) {
@@ -300,6 +303,8 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   c->bvh_info.build_ms = bvh.build_ms;
   c->bvh_info.sah_cost = bvh.sah_cost;
   c->graph_depth = fs.graph_depth;
+  c->kinds_present = 0;
+  for (uint32_t i = 0; i < d->n_materials; i++) c->kinds_present |= 1u << d->materials[i].kind;
   c->have_scene = true;
   return B200RT_OK;
 }
@@ -457,9 +462,13 @@ int ensure_wave(b200rt_ctx *c, uint32_t capacity, bool mirror) {
   return B200RT_OK;
 }
 
+// one launch per queue that can be non-empty in this scene; returns the number of launches
 template <bool MIRROR>
-void launch_shades(b200rt_ctx *c, cudaStream_t s, int grid, const PathBuf &cur, const PathBuf &nxt, double *accum, const WaveParams &wp) {
-#define SHADE(K) k_shade<K, MIRROR><<<grid, 128, 0, s>>>(c->ctl, c->S, cur, nxt, c->hits, c->recs, c->queues.q[K], accum, wp)
+int launch_shades(b200rt_ctx *c, cudaStream_t s, int grid, const PathBuf &cur, const PathBuf &nxt, double *accum, const WaveParams &wp) {
+  int n = 0;
+#define SHADE(K)                                                                                                       \
+  if (K == B200_Q_MISS || (c->kinds_present >> K & 1u))                                                                \
+  n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(c->ctl, c->S, cur, nxt, c->hits, c->recs, c->queues.q[K], accum, wp)
   SHADE(B200_Q_MISS);
   SHADE(B200RT_MAT_DIFFUSE_LIGHT);
   SHADE(B200RT_MAT_LAMBERTIAN);
@@ -468,6 +477,7 @@ void launch_shades(b200rt_ctx *c, cudaStream_t s, int grid, const PathBuf &cur, 
   SHADE(B200RT_MAT_GLOSS);
   SHADE(B200RT_MAT_ISOTROPIC);
 #undef SHADE
+  return n;
 }
 
 } // namespace
@@ -501,7 +511,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   wp.spp_begin = spp_begin;
   wp.max_depth = c->cam.max_depth;
   wp.kill_zero = c->kill_zero;
-  wp.refill = c->refill_lanes;
+  wp.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 16 : 32);
   for (int k = 0; k < 3; k++) wp.bound[k] = c->S.bound[k];
   const DevCamera cam = make_camera(c->cam);
   const int g_gen = grid_for(c, capacity, 256, 8), g_ext = grid_for(c, capacity, 128, 16);
@@ -525,20 +535,22 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     if (mirror)
       k_extend<true><<<g_ext, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->recs, c->queues, wp);
     else
-      switch (c->extend_blocks) {
-      case 5: k_extend_persistent<5><<<c->sm_count * 5, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
-      case 6: k_extend_persistent<6><<<c->sm_count * 6, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
-      case 8: k_extend_persistent<8><<<c->sm_count * 8, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
-      default: k_extend_persistent<4><<<c->sm_count * 4, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, wp); break;
+      switch (c->extend_blocks * 2 + (c->speculative ? 1 : 0)) {
+      // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
+#define EXT(MAXREG, SPEC, WARPS) k_extend_persistent<MAXREG, SPEC, WARPS><<<c->sm_count * (65536 / (MAXREG * WARPS * 32)), WARPS * 32, 0, s>>>(c->ctl, c->S, cur, c->hits, wp)
+      case 12: EXT(80, false, 4); break;  // 24 warps per SM
+      case 10: EXT(96, false, 2); break;  // 20 warps
+      case 18: EXT(112, false, 2); break; // 18 warps (option value 9: 2-warp CTAs)
+      case 34: EXT(120, false, 1); break; // 17 warps (option value 17: 1-warp CTAs)
+      case 9: EXT(128, true, 4); break;
+      default: EXT(128, false, 4); break; // 16 warps
+#undef EXT
       }
     if (stats) CU(cudaEventRecord(ext_events.back(), s));
     if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(c->ctl, c->hits, c->queues);
-    if (mirror)
-      launch_shades<true>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
-    else
-      launch_shades<false>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
+    const int n_shade = mirror ? launch_shades<true>(c, s, g_ext, cur, nxt, d_rgb_sum, wp) : launch_shades<false>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
     k_ctl_swap<<<1, 1, 0, s>>>(c->ctl);
-    launches += (mirror ? 4 : 5) + B200_NQUEUES;
+    launches += (mirror ? 4 : 5) + n_shade;
     wave++;
     if (wave >= next_check) {
       CU(cudaMemcpyAsync(c->h_ctl, c->ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, s));

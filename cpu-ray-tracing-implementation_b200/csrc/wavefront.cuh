@@ -244,13 +244,23 @@ DEV void cp_async_wait_all() {
 // {t, leaf} itself; sorting into material queues is a separate coalesced pass (k_classify).
 // Inner structure: "while nodes / then one leaf" so that the binary32 box filter and the binary64 leaf tests each
 // run with as many lanes as possible.
-template <int MINB>
-__global__ void __launch_bounds__(128, MINB) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp) {
-  __shared__ __align__(16) double2 stage_mem[4][2][B200_EXT_QUADS][32]; // warp x stage x quad x lane: 28 KB
+// SPEC: speculative traversal — a lane that reaches its first leaf postpones it and keeps walking inner nodes until it
+// meets a second leaf (or runs out), so that the node phase and the leaf phase of a warp each run with more lanes; the price
+// is that the postponed leaf has not yet shrunk the interval for the nodes walked in between.
+// WARPS x MINB = resident warps per SM the kernel is compiled for: registers are handed out per warp, so 2-warp CTAs give
+// occupancy points (18 warps at 112 registers) that 4-warp CTAs skip.
+#ifdef B200_HOST_EMU
+#define B200_MAXNREG(n)
+#else
+#define B200_MAXNREG(n) __maxnreg__(n)
+#endif
+template <int MAXREG, bool SPEC, int WARPS>
+__global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp) {
+  __shared__ __align__(16) double2 stage_mem[WARPS][2][B200_EXT_QUADS][32]; // warp x stage x quad x lane: 7 KB per warp
   const uint32_t n = c->n_cur;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const unsigned FULL = 0xffffffffu;
-  const uint32_t n_warps = gridDim.x * 4, n_batches = (n + 31) / 32;
+  const uint32_t n_warps = gridDim.x * WARPS, n_batches = (n + 31) / 32;
   const int refill = wp.refill, keep = 33 - wp.refill;
 
   auto prefetch = [&](int stg, uint32_t batch) { // one cp.async group per call, also when there is nothing to copy
@@ -262,7 +272,7 @@ __global__ void __launch_bounds__(128, MINB) k_extend_persistent(const WaveCtl *
     cp_async_commit();
   };
 
-  uint32_t batch = blockIdx.x * 4 + wib; // the batch staged in `stg`
+  uint32_t batch = blockIdx.x * WARPS + wib; // the batch staged in `stg`
   int stg = 0;
   prefetch(0, batch);
   prefetch(1, batch + n_warps);
@@ -332,14 +342,38 @@ __global__ void __launch_bounds__(128, MINB) k_extend_persistent(const WaveCtl *
       continue;
     }
     while (active) {
-      while (node >= 0) {
-        node = node_step(S, node, rs, lo32, hi32, stack, sp);
-        if (node == B200_DONE && sp > 0) node = stack[--sp];
-      }
-      if (node != B200_DONE) {
-        leaf_test(S, node, r, 0.001, B200_INF, st, bounce, best);
-        if (best.entry >= 0) hi32 = __double2float_ru(best.t * rs.tsc);
-        node = sp > 0 ? stack[--sp] : B200_DONE;
+      if (SPEC) {
+        int32_t pending = B200_DONE;
+        for (;;) {
+          if (node < 0) { // a leaf or the end
+            if (node == B200_DONE || pending != B200_DONE) break;
+            pending = node;
+            node = sp > 0 ? stack[--sp] : B200_DONE;
+            continue;
+          }
+          node = node_step(S, node, rs, lo32, hi32, stack, sp);
+          if (node == B200_DONE && sp > 0) node = stack[--sp];
+        }
+        while (pending != B200_DONE) { // the postponed leaf, then whatever leaves follow directly
+          leaf_test(S, pending, r, 0.001, B200_INF, st, bounce, best);
+          if (best.entry >= 0) hi32 = __double2float_ru(best.t * rs.tsc);
+          if (node < 0 && node != B200_DONE) {
+            pending = node;
+            node = sp > 0 ? stack[--sp] : B200_DONE;
+          } else {
+            pending = B200_DONE;
+          }
+        }
+      } else {
+        while (node >= 0) {
+          node = node_step(S, node, rs, lo32, hi32, stack, sp);
+          if (node == B200_DONE && sp > 0) node = stack[--sp];
+        }
+        if (node != B200_DONE) {
+          leaf_test(S, node, r, 0.001, B200_INF, st, bounce, best);
+          if (best.entry >= 0) hi32 = __double2float_ru(best.t * rs.tsc);
+          node = sp > 0 ? stack[--sp] : B200_DONE;
+        }
       }
       if (node == B200_DONE) {
         if (best.entry < 0)

@@ -216,12 +216,13 @@ typedef struct b200rt_camera {
 /* ------------------------------------------------------------------ options */
 typedef enum b200rt_option {
   B200RT_OPT_TRAVERSAL = 0,     /* 0 = compacted SAH BVH (default), 1 = node-for-node mirror of the reference graph */
-  B200RT_OPT_WAVE_PATHS = 1,    /* paths resident per wave (default 4 Mi)        */
+  B200RT_OPT_WAVE_PATHS = 1,    /* paths resident per wave (default 16 Mi = 5 GB of wavefront state) */
   B200RT_OPT_KILL_ZERO_WEIGHT = 2, /* 1 (default): drop paths whose throughput is exactly 0 in all channels */
-  B200RT_OPT_BVH_LEAF_SIZE = 3, /* max primitives per leaf of the compacted BVH  */
+  B200RT_OPT_BVH_LEAF_SIZE = 3, /* max primitives per leaf of the compacted BVH; 0 (default) = 1 up to 8192 primitives, else 2 */
   B200RT_OPT_SMEM_NODES = 4,    /* top-of-tree nodes staged in shared memory (reserved) */
-  B200RT_OPT_EXTEND_BLOCKS = 6, /* tuning: resident CTAs per SM the persistent extend kernel is compiled for (4, 5, 6 or 8) */
-  B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (default 32 = fixed 32-ray batches, measured fastest on RTOW) */
+  B200RT_OPT_EXTEND_BLOCKS = 6, /* tuning: resident CTAs per SM the persistent extend kernel is compiled for (4 or 6; 6 spills and is slower: profiles/r01_g_tune.txt) */
+  B200RT_OPT_SPECULATIVE_LEAF = 7, /* tuning: 1 = a lane postpones its first leaf and keeps walking inner nodes (speculative traversal) */
+  B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 16 from 32 Ki BVH nodes) */
 } b200rt_option;
 
 #define B200RT_TRAVERSAL_FAST 0

@@ -188,9 +188,33 @@ def test_sample_ranges_add_up_and_wave_size_is_irrelevant(ctx):
     assert np.allclose(whole, a + b, rtol=1e-12, atol=1e-12)
     ctx.set_option(abi.OPT_WAVE_PATHS, 4096)
     small, st2 = ctx.render(1234, 0, 24)
-    ctx.set_option(abi.OPT_WAVE_PATHS, 1 << 22)
+    ctx.set_option(abi.OPT_WAVE_PATHS, 1 << 24)
     assert np.allclose(whole, small, rtol=1e-12, atol=1e-12)
     assert st["rays"] == st2["rays"] and st["samples"] == st2["samples"] == 24 * g.cam_small.image_width * g.cam_small.image_height
+
+
+@pytest.mark.parametrize("name", ["rtow", "rtnw", "fox", "cornell_volume"])
+def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
+    """Lane refill and speculative (postponed-leaf) traversal change the order in which leaves are tested, never the hit:
+    same rays, same samples, same sums (up to fp64 atomic order)."""
+    g = golden(name)
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(g.cam_small)
+    base, st = ctx.render(77, 0, 6)
+    try:
+        for opts in ({abi.OPT_SPECULATIVE_LEAF: 1}, {abi.OPT_REFILL_LANES: 12}, {abi.OPT_SPECULATIVE_LEAF: 1, abi.OPT_REFILL_LANES: 20}):
+            for k, v in opts.items():
+                ctx.set_option(k, v)
+            img, st2 = ctx.render(77, 0, 6)
+            ctx.set_option(abi.OPT_SPECULATIVE_LEAF, 0)
+            ctx.set_option(abi.OPT_REFILL_LANES, 0)
+            assert st2["rays"] == st["rays"], opts
+            fin = np.isfinite(base)
+            assert np.array_equal(fin, np.isfinite(img))
+            assert np.allclose(base[fin], img[fin], rtol=1e-12, atol=1e-12), opts
+    finally:
+        ctx.set_option(abi.OPT_SPECULATIVE_LEAF, 0)
+        ctx.set_option(abi.OPT_REFILL_LANES, 0)
 
 
 def test_white_furnace_known_answer(ctx):

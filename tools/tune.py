@@ -37,6 +37,7 @@ def main():
     ap.add_argument("--refill", default="32")
     ap.add_argument("--blocks", default="4")
     ap.add_argument("--leaf", default="2")
+    ap.add_argument("--spec", default="0", help="speculative (postponed-leaf) traversal: 0, 1 or 0,1")
     a = ap.parse_args()
     scene, cam = load(a.scene)
     H, W = cam.image_height, cam.image_width
@@ -47,7 +48,8 @@ def main():
         ctx.set_option(abi.OPT_BVH_LEAF_SIZE, leaf)
         ctx.upload_scene(scene)
         ctx.set_camera(cam)
-        for wave, refill, blocks in itertools.product(ints(a.wave), ints(a.refill), ints(a.blocks)):
+        for wave, refill, blocks, spec in itertools.product(ints(a.wave), ints(a.refill), ints(a.blocks), ints(a.spec)):
+            ctx.set_option(abi.OPT_SPECULATIVE_LEAF, spec)
             ctx.set_option(abi.OPT_WAVE_PATHS, 1 << wave)
             ctx.set_option(abi.OPT_REFILL_LANES, refill)
             ctx.set_option(abi.OPT_EXTEND_BLOCKS, blocks)
@@ -57,7 +59,7 @@ def main():
                 st = ctx.render_device(0x5EED, 0, a.spp, accum.data_ptr(), stream, want_stats=True)
                 if best is None or st["gpu_ms"] < best["gpu_ms"]:
                     best = st
-            print(json.dumps({"scene": a.scene, "spp": a.spp, "leaf": leaf, "wave_log2": wave, "refill": refill, "blocks": blocks,
+            print(json.dumps({"scene": a.scene, "spp": a.spp, "leaf": leaf, "wave_log2": wave, "refill": refill, "blocks": blocks, "spec": spec,
                               "mrays_per_s": best["rays"] / best["gpu_ms"] / 1e3, "gpu_ms": best["gpu_ms"], "extend_ms": best["extend_ms"],
                               "waves": best["waves"]}), flush=True)
         ctx.close()
