@@ -153,6 +153,8 @@ def run_ours(args):
         ctx.set_option(abi.OPT_BVH_LEAF_SIZE, args.leaf)
     if args.extend_blocks:
         ctx.set_option(abi.OPT_EXTEND_BLOCKS, args.extend_blocks)
+    if args.no_fuse_miss:
+        ctx.set_option(abi.OPT_FUSE_MISS, 0)
     ctx.upload_scene(scene)
     ctx.set_camera(cam)
     accum = torch.zeros(H * W * 3, dtype=torch.float64, device="cuda")
@@ -255,6 +257,7 @@ if __name__ == "__main__":
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--refill", type=int, default=0, help="tuning: idle lanes per warp that trigger a ray fetch in the persistent extend kernel")
     ap.add_argument("--extend-blocks", type=int, default=0, help="tuning: CTAs/SM of the persistent extend kernel (4, 5, 6, 8)")
+    ap.add_argument("--no-fuse-miss", action="store_true", help="tuning: send missing rays through the miss queue and its shade launch")
     ap.add_argument("--leaf", type=int, default=0, help="tuning: max primitives per BVH leaf")
     a = ap.parse_args()
     if a.impl == "reference":

@@ -62,6 +62,9 @@ struct b200rt_ctx {
   int refill_lanes = 0; // 0 = by BVH size: fixed 32-ray batches for cache-resident trees, refill at 16 idle lanes from 32 Ki nodes
   int extend_blocks = 4;
   int speculative = 0;
+  int fuse_miss = 1;
+  int extend_stages = 2; // 1 is within 1 % on RTOW / RTNW / Cornell and 11 % slower on Fox (profiles/r01_h_tune_l1.txt)
+  int carveout_pct = -1; // -1 = computed from the kernel's footprint
   // scene
   bool have_scene = false, have_camera = false;
   DevMem scene_mem;
@@ -69,6 +72,7 @@ struct b200rt_ctx {
   b200rt_bvh_info bvh_info{};
   double scene_h2d_bytes = 0;
   int graph_depth = 0;
+  int bg_mode = 0; // WaveParams::fused_miss for this scene
   uint32_t kinds_present = 0; // bit k: some material of the scene has b200rt_material_kind k (queues of absent kinds stay empty)
   // camera
   b200rt_camera cam{};
@@ -215,6 +219,15 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
   case B200RT_OPT_SMEM_NODES: return B200RT_OK; // reserved
   case B200RT_OPT_EXTEND_BLOCKS: c->extend_blocks = (int)value; return B200RT_OK;
   case B200RT_OPT_SPECULATIVE_LEAF: c->speculative = value != 0; return B200RT_OK;
+  case B200RT_OPT_FUSE_MISS: c->fuse_miss = value != 0; return B200RT_OK;
+  case B200RT_OPT_EXTEND_STAGES:
+    if (value != 1 && value != 2) return fail(B200RT_ERR_INVALID, "extend stages must be 1 or 2");
+    c->extend_stages = (int)value;
+    return B200RT_OK;
+  case B200RT_OPT_SMEM_CARVEOUT:
+    if (!(value >= -1 && value <= 100)) return fail(B200RT_ERR_INVALID, "carve-out must be -1 (automatic) or a percentage");
+    c->carveout_pct = (int)value;
+    return B200RT_OK;
   case B200RT_OPT_REFILL_LANES:
     if (!(value >= 0 && value <= 32)) return fail(B200RT_ERR_INVALID, "refill lanes must be in [0, 32] (0 = automatic)");
     c->refill_lanes = (int)value;
@@ -305,6 +318,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   c->graph_depth = fs.graph_depth;
   c->kinds_present = 0;
   for (uint32_t i = 0; i < d->n_materials; i++) c->kinds_present |= 1u << d->materials[i].kind;
+  c->bg_mode = d->background_tex < 0 ? 1 : 0;
   c->have_scene = true;
   return B200RT_OK;
 }
@@ -463,11 +477,19 @@ int ensure_wave(b200rt_ctx *c, uint32_t capacity, bool mirror) {
 }
 
 // one launch per queue that can be non-empty in this scene; returns the number of launches
+// Persistent extend launch.  The shared-memory carve-out is requested explicitly (smallest configuration that holds the
+// resident CTAs): what is left of the 256 KB is the L1 that caches BVH nodes and primitives.
+template <class K> void launch_extend(K kernel, b200rt_ctx *c, int ctas_per_sm, int threads, int smem_per_cta, cudaStream_t s, const PathBuf &cur, const WaveParams &wp) {
+  const int want_kb = (ctas_per_sm * (smem_per_cta + 1024) + 1023) / 1024;
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, c->carveout_pct >= 0 ? c->carveout_pct : std::min(100, (want_kb * 100 + 227) / 228));
+  kernel<<<c->sm_count * ctas_per_sm, threads, 0, s>>>(c->ctl, c->S, cur, c->hits, wp);
+}
+
 template <bool MIRROR>
 int launch_shades(b200rt_ctx *c, cudaStream_t s, int grid, const PathBuf &cur, const PathBuf &nxt, double *accum, const WaveParams &wp) {
   int n = 0;
 #define SHADE(K)                                                                                                       \
-  if (K == B200_Q_MISS || (c->kinds_present >> K & 1u))                                                                \
+  if (K == B200_Q_MISS ? wp.fused_miss == 0 : (c->kinds_present >> K & 1u))                                                                \
   n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(c->ctl, c->S, cur, nxt, c->hits, c->recs, c->queues.q[K], accum, wp)
   SHADE(B200_Q_MISS);
   SHADE(B200RT_MAT_DIFFUSE_LIGHT);
@@ -511,6 +533,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   wp.spp_begin = spp_begin;
   wp.max_depth = c->cam.max_depth;
   wp.kill_zero = c->kill_zero;
+  wp.fused_miss = (mirror || !c->fuse_miss) ? 0 : c->bg_mode;
   wp.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 16 : 32);
   for (int k = 0; k < 3; k++) wp.bound[k] = c->S.bound[k];
   const DevCamera cam = make_camera(c->cam);
@@ -537,13 +560,18 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     else
       switch (c->extend_blocks * 2 + (c->speculative ? 1 : 0)) {
       // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
-#define EXT(MAXREG, SPEC, WARPS) k_extend_persistent<MAXREG, SPEC, WARPS><<<c->sm_count * (65536 / (MAXREG * WARPS * 32)), WARPS * 32, 0, s>>>(c->ctl, c->S, cur, c->hits, wp)
-      case 12: EXT(80, false, 4); break;  // 24 warps per SM
-      case 10: EXT(96, false, 2); break;  // 20 warps
-      case 18: EXT(112, false, 2); break; // 18 warps (option value 9: 2-warp CTAs)
-      case 34: EXT(120, false, 1); break; // 17 warps (option value 17: 1-warp CTAs)
-      case 9: EXT(128, true, 4); break;
-      default: EXT(128, false, 4); break; // 16 warps
+#define EXT(MAXREG, SPEC, WARPS, STAGES)                                                                               \
+  launch_extend(k_extend_persistent<MAXREG, SPEC, WARPS, STAGES>, c, 65536 / (MAXREG * WARPS * 32), WARPS * 32, WARPS * STAGES * 3584, s, cur, wp)
+      case 12: EXT(80, false, 4, 2); break;  // 24 warps per SM
+      case 10: EXT(96, false, 2, 2); break;  // 20 warps
+      case 18: EXT(112, false, 2, 2); break; // 18 warps (option value 9: 2-warp CTAs)
+      case 9: EXT(128, true, 4, 2); break;
+      default:
+        if (c->extend_stages == 1 && wp.refill == 32)
+          EXT(128, false, 4, 1);
+        else
+          EXT(128, false, 4, 2);
+        break; // 16 warps
 #undef EXT
       }
     if (stats) CU(cudaEventRecord(ext_events.back(), s));

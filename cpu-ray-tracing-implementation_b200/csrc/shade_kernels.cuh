@@ -5,12 +5,6 @@
 
 namespace b200 {
 
-DEV void accumulate(double *accum, uint32_t pixel, V c) { // image_[i*W+j] += sample, src/camera.h:167-169
-  if (c.x != 0.0) atomicAdd(accum + 3 * (size_t)pixel, c.x);
-  if (c.y != 0.0) atomicAdd(accum + 3 * (size_t)pixel + 1, c.y);
-  if (c.z != 0.0) atomicAdd(accum + 3 * (size_t)pixel + 2, c.z);
-}
-
 // One launch per queue.  KIND = b200rt_material_kind of every hit in the queue, or B200_Q_MISS.
 template <int KIND, bool MIRROR>
 __global__ void __launch_bounds__(128) k_shade(WaveCtl *c, DevScene S, PathBuf cur, PathBuf nxt, const HitRef *hits, const Rec *recs,

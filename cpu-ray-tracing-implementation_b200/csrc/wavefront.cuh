@@ -19,6 +19,7 @@ namespace b200 {
 
 #define B200_NQUEUES 7 /* six material kinds (b200rt_material_kind) + miss */
 #define B200_Q_MISS 6
+#define B200_Q_MISS_DONE 7 /* a miss that the extend kernel has already accounted for (WaveParams::fused_miss): counted, never queued */
 #define B200_DEAD 0xFFFFFFFFu
 
 struct WaveCtl {
@@ -45,6 +46,7 @@ struct WaveParams {
   uint64_t seed;
   uint32_t npix, width;
   int32_t spp_begin, max_depth, kill_zero, refill; // refill: idle lanes per warp that trigger a fetch in k_extend_persistent
+  int32_t fused_miss; // 1 = the scene has no background: a miss adds 0, the extend kernel finishes it itself (no miss queue, no miss launch)
   double bound[3]; // DevScene::bound, for the producers' make_setup
 };
 
@@ -124,7 +126,7 @@ __global__ void k_ctl_generated(WaveCtl *c) {
 }
 __global__ void k_ctl_swap(WaveCtl *c) {
   unsigned long long r = 0;
-  for (int k = 0; k < B200_NQUEUES; k++) r += c->q_count[k], c->q_count[k] = 0;
+  for (int k = 0; k < 8; k++) r += c->q_count[k], c->q_count[k] = 0; // 7 queues + misses finished inside extend
   c->rays += r;
   c->n_cur = c->n_next;
   c->n_next = 0;
@@ -217,6 +219,11 @@ __global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, PathBuf 
 
 
 // ------------------------------------------------------------------------------------------------ persistent extend
+DEV void accumulate(double *accum, uint32_t pixel, V c) { // image_[i*W+j] += sample, src/camera.h:167-169
+  if (c.x != 0.0) atomicAdd(accum + 3 * (size_t)pixel, c.x);
+  if (c.y != 0.0) atomicAdd(accum + 3 * (size_t)pixel + 1, c.y);
+  if (c.z != 0.0) atomicAdd(accum + 3 * (size_t)pixel + 2, c.z);
+}
 DEV void cp_async16(void *smem_dst, const void *gmem_src) {
 #ifndef B200_HOST_EMU
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -254,9 +261,12 @@ DEV void cp_async_wait_all() {
 #else
 #define B200_MAXNREG(n) __maxnreg__(n)
 #endif
-template <int MAXREG, bool SPEC, int WARPS>
+// STAGES: 2 = the next batch is always in flight (needed when lanes refill mid-batch); 1 = the single stage is refilled as
+// soon as its 32 rays have been taken into registers.  Shared memory is carved out of the L1 that caches the BVH, so the
+// smaller footprint (14 KB instead of 28 KB per CTA) is not free to give away: see DESIGN.md.
+template <int MAXREG, bool SPEC, int WARPS, int STAGES>
 __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp) {
-  __shared__ __align__(16) double2 stage_mem[WARPS][2][B200_EXT_QUADS][32]; // warp x stage x quad x lane: 7 KB per warp
+  __shared__ __align__(16) double2 stage_mem[WARPS][STAGES][B200_EXT_QUADS][32]; // warp x stage x quad x lane: 3.5 KB per warp and stage
   const uint32_t n = c->n_cur;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const unsigned FULL = 0xffffffffu;
@@ -272,13 +282,17 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
     cp_async_commit();
   };
 
+  // A ray that hits nothing.  Without a background camera::miss adds exactly 0 (src/camera.h:181): the path is finished
+  // here (counted, never queued) and the scene needs no miss launch at all.
+  auto finish_miss = [&](uint32_t i) { store_hit(hits, i, 0.0, -1, wp.fused_miss ? B200_Q_MISS_DONE : B200_Q_MISS); };
+
   uint32_t batch = blockIdx.x * WARPS + wib; // the batch staged in `stg`
   int stg = 0;
   prefetch(0, batch);
-  prefetch(1, batch + n_warps);
   cp_async_wait_all();
   __syncwarp();
   uint32_t base = batch * 32, count = batch < n_batches ? min(32u, n - base) : 0u, taken = 0;
+  if (STAGES == 2) prefetch(1, batch + n_warps);
 
   bool active = false;
   uint32_t idx = 0;
@@ -295,14 +309,14 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
     unsigned idle = __ballot_sync(FULL, !active);
     if (count > 0 && (__popc(idle) >= refill || idle == FULL)) {
       while (idle != 0 && count > 0) {
-        if (taken == count) { // next staged batch; refill the stage just drained
+        if (taken == count) { // next staged batch (already in flight)
           const int drained = stg;
           batch += n_warps;
-          stg ^= 1;
+          if (STAGES == 2) stg ^= 1;
           cp_async_wait_all();
           __syncwarp();
           base = batch * 32, count = batch < n_batches ? min(32u, n - base) : 0u, taken = 0;
-          prefetch(drained, batch + n_warps);
+          if (STAGES == 2) prefetch(drained, batch + n_warps); // refill the stage just drained
           continue;
         }
         const uint32_t slot = taken + (uint32_t)__popc(idle & ((1u << lane) - 1u));
@@ -330,10 +344,14 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
             sp = 0;
             node = S.bvh_root;
             active = node != B200_EMPTY_ROOT;
-            if (!active) store_hit(hits, idx, 0.0, -1, B200_Q_MISS);
+            if (!active) finish_miss(idx);
           }
         }
         taken += min((uint32_t)__popc(idle), count - taken);
+        if (STAGES == 1 && taken == count) { // every ray of the stage is in registers now: start fetching the next batch into it
+          __syncwarp();
+          prefetch(0, batch + n_warps);
+        }
         idle = __ballot_sync(FULL, !active);
       }
     }
@@ -377,7 +395,7 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
       }
       if (node == B200_DONE) {
         if (best.entry < 0)
-          store_hit(hits, idx, 0.0, -1, B200_Q_MISS);
+          finish_miss(idx);
         else
           store_hit(hits, idx, best.t, best.entry, S.materials[entry_material(S, S.entries[best.entry])].kind);
         active = false;
@@ -395,12 +413,12 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
 // range of every queue with ONE global atomic per queue per chunk.
 #define B200_CLASSIFY_K 8
 __global__ void __launch_bounds__(256) k_classify(WaveCtl *c, const HitRef *hits, Queues Q) {
-  __shared__ uint32_t s_count[B200_NQUEUES], s_base[B200_NQUEUES];
+  __shared__ uint32_t s_count[B200_NQUEUES + 1], s_base[B200_NQUEUES]; // [B200_Q_MISS_DONE]: counted only
   const uint32_t n = c->n_cur;
   const int lane = threadIdx.x & 31;
   const uint32_t chunk = 256 * B200_CLASSIFY_K;
   for (uint32_t cbase = blockIdx.x * chunk; cbase < n; cbase += gridDim.x * chunk) {
-    if (threadIdx.x < B200_NQUEUES) s_count[threadIdx.x] = 0;
+    if (threadIdx.x <= B200_NQUEUES) s_count[threadIdx.x] = 0;
     __syncthreads();
     int which[B200_CLASSIFY_K];
     uint32_t rank[B200_CLASSIFY_K];
@@ -409,6 +427,11 @@ __global__ void __launch_bounds__(256) k_classify(WaveCtl *c, const HitRef *hits
       const uint32_t i = cbase + k * 256 + threadIdx.x;
       which[k] = i < n ? __ldg(reinterpret_cast<const int4 *>(hits + i)).w : -1;
       rank[k] = 0;
+      {
+        const unsigned m = __ballot_sync(0xffffffffu, which[k] == B200_Q_MISS_DONE);
+        if (m != 0 && lane == 0) atomicAdd(&s_count[B200_Q_MISS_DONE], (uint32_t)__popc(m));
+        if (which[k] == B200_Q_MISS_DONE) which[k] = -1;
+      }
 #pragma unroll
       for (int q = 0; q < B200_NQUEUES; q++) {
         const unsigned m = __ballot_sync(0xffffffffu, which[k] == q);
@@ -421,6 +444,7 @@ __global__ void __launch_bounds__(256) k_classify(WaveCtl *c, const HitRef *hits
     }
     __syncthreads();
     if (threadIdx.x < B200_NQUEUES) s_base[threadIdx.x] = s_count[threadIdx.x] ? atomicAdd(&c->q_count[threadIdx.x], s_count[threadIdx.x]) : 0;
+    if (threadIdx.x == B200_NQUEUES && s_count[B200_NQUEUES]) atomicAdd(&c->q_count[B200_NQUEUES], s_count[B200_NQUEUES]);
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < B200_CLASSIFY_K; k++)

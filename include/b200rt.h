@@ -222,6 +222,9 @@ typedef enum b200rt_option {
   B200RT_OPT_SMEM_NODES = 4,    /* top-of-tree nodes staged in shared memory (reserved) */
   B200RT_OPT_EXTEND_BLOCKS = 6, /* tuning: resident CTAs per SM the persistent extend kernel is compiled for (4 or 6; 6 spills and is slower: profiles/r01_g_tune.txt) */
   B200RT_OPT_SPECULATIVE_LEAF = 7, /* tuning: 1 = a lane postpones its first leaf and keeps walking inner nodes (speculative traversal) */
+  B200RT_OPT_FUSE_MISS = 8,     /* 1 (default): in a scene without background the extend kernel finishes a miss itself (it adds 0) instead of queueing the path */
+  B200RT_OPT_EXTEND_STAGES = 9, /* tuning: ray batches staged in shared memory per warp, 2 (default) or 1; lane refill always uses 2 */
+  B200RT_OPT_SMEM_CARVEOUT = 10, /* tuning: shared-memory carve-out of the extend kernel in percent, -1 (default) = smallest that fits */
   B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 16 from 32 Ki BVH nodes) */
 } b200rt_option;
 

@@ -193,7 +193,7 @@ def test_sample_ranges_add_up_and_wave_size_is_irrelevant(ctx):
     assert st["rays"] == st2["rays"] and st["samples"] == st2["samples"] == 24 * g.cam_small.image_width * g.cam_small.image_height
 
 
-@pytest.mark.parametrize("name", ["rtow", "rtnw", "fox", "cornell_volume"])
+@pytest.mark.parametrize("name", ["rtow", "rtnw", "fox", "cornell_volume", "three_ball_lens", "skybox_fisheye"])
 def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
     """Lane refill and speculative (postponed-leaf) traversal change the order in which leaves are tested, never the hit:
     same rays, same samples, same sums (up to fp64 atomic order)."""
@@ -202,12 +202,17 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
     ctx.set_camera(g.cam_small)
     base, st = ctx.render(77, 0, 6)
     try:
-        for opts in ({abi.OPT_SPECULATIVE_LEAF: 1}, {abi.OPT_REFILL_LANES: 12}, {abi.OPT_SPECULATIVE_LEAF: 1, abi.OPT_REFILL_LANES: 20}):
+        for opts in ({abi.OPT_SPECULATIVE_LEAF: 1}, {abi.OPT_REFILL_LANES: 12}, {abi.OPT_SPECULATIVE_LEAF: 1, abi.OPT_REFILL_LANES: 20}, {abi.OPT_FUSE_MISS: 0},
+                     {abi.OPT_EXTEND_BLOCKS: 9}, {abi.OPT_EXTEND_STAGES: 1}, {abi.OPT_SMEM_CARVEOUT: 100}):
             for k, v in opts.items():
                 ctx.set_option(k, v)
             img, st2 = ctx.render(77, 0, 6)
             ctx.set_option(abi.OPT_SPECULATIVE_LEAF, 0)
             ctx.set_option(abi.OPT_REFILL_LANES, 0)
+            ctx.set_option(abi.OPT_FUSE_MISS, 1)
+            ctx.set_option(abi.OPT_EXTEND_BLOCKS, 4)
+            ctx.set_option(abi.OPT_EXTEND_STAGES, 2)
+            ctx.set_option(abi.OPT_SMEM_CARVEOUT, -1)
             assert st2["rays"] == st["rays"], opts
             fin = np.isfinite(base)
             assert np.array_equal(fin, np.isfinite(img))
@@ -215,6 +220,10 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
     finally:
         ctx.set_option(abi.OPT_SPECULATIVE_LEAF, 0)
         ctx.set_option(abi.OPT_REFILL_LANES, 0)
+        ctx.set_option(abi.OPT_FUSE_MISS, 1)
+        ctx.set_option(abi.OPT_EXTEND_BLOCKS, 4)
+        ctx.set_option(abi.OPT_EXTEND_STAGES, 2)
+        ctx.set_option(abi.OPT_SMEM_CARVEOUT, -1)
 
 
 def test_white_furnace_known_answer(ctx):

@@ -22,7 +22,7 @@ abi = pkg._abi
 
 
 def ints(s):
-    return [int(x) for x in s.split(",") if x]
+    return [int(x) for x in s.replace("m", "-").split(",") if x]
 
 
 def main():
@@ -33,10 +33,12 @@ def main():
     ap.add_argument("--scene", default="rtow")
     ap.add_argument("--spp", type=int, default=32)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--wave", default="22")
-    ap.add_argument("--refill", default="32")
+    ap.add_argument("--wave", default="24")
+    ap.add_argument("--refill", default="0")
     ap.add_argument("--blocks", default="4")
-    ap.add_argument("--leaf", default="2")
+    ap.add_argument("--leaf", default="0")
+    ap.add_argument("--stages", default="1", help="ray batches staged per warp: 1, 2 or 1,2")
+    ap.add_argument("--carveout", default="-1", help="shared-memory carve-out percent of the extend kernel (-1 = automatic)")
     ap.add_argument("--spec", default="0", help="speculative (postponed-leaf) traversal: 0, 1 or 0,1")
     a = ap.parse_args()
     scene, cam = load(a.scene)
@@ -48,8 +50,11 @@ def main():
         ctx.set_option(abi.OPT_BVH_LEAF_SIZE, leaf)
         ctx.upload_scene(scene)
         ctx.set_camera(cam)
-        for wave, refill, blocks, spec in itertools.product(ints(a.wave), ints(a.refill), ints(a.blocks), ints(a.spec)):
+        for wave, refill, blocks, spec, stages, carve in itertools.product(ints(a.wave), ints(a.refill), ints(a.blocks), ints(a.spec), ints(a.stages),
+                                                                           ints(a.carveout)):
             ctx.set_option(abi.OPT_SPECULATIVE_LEAF, spec)
+            ctx.set_option(abi.OPT_EXTEND_STAGES, stages)
+            ctx.set_option(abi.OPT_SMEM_CARVEOUT, carve)
             ctx.set_option(abi.OPT_WAVE_PATHS, 1 << wave)
             ctx.set_option(abi.OPT_REFILL_LANES, refill)
             ctx.set_option(abi.OPT_EXTEND_BLOCKS, blocks)
@@ -59,7 +64,7 @@ def main():
                 st = ctx.render_device(0x5EED, 0, a.spp, accum.data_ptr(), stream, want_stats=True)
                 if best is None or st["gpu_ms"] < best["gpu_ms"]:
                     best = st
-            print(json.dumps({"scene": a.scene, "spp": a.spp, "leaf": leaf, "wave_log2": wave, "refill": refill, "blocks": blocks, "spec": spec,
+            print(json.dumps({"scene": a.scene, "spp": a.spp, "leaf": leaf, "wave_log2": wave, "refill": refill, "blocks": blocks, "spec": spec, "stages": stages, "carveout": carve,
                               "mrays_per_s": best["rays"] / best["gpu_ms"] / 1e3, "gpu_ms": best["gpu_ms"], "extend_ms": best["extend_ms"],
                               "waves": best["waves"]}), flush=True)
         ctx.close()
