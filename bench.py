@@ -27,7 +27,7 @@ sys.path.insert(0, ROOT)
 SCENE = "rtow"
 WORKLOAD = "RTOW final scene: 487 spheres (lambertian/metal/dielectric), lens DOF camera, 1200x675, 500 spp, max depth 50"
 METRIC, UNIT = "Mrays/s on RTOW final scene (1200x675, 500 spp, depth 50); Msamples/s alongside", "Mrays/s"
-TRAFFIC_BYTES_PER_LAUNCH = 528.97e6  # profiles/r01_e_extend.txt: dram__bytes_read.sum 470.5 MB + dram__bytes_write.sum 58.5 MB (4 Mi-ray launch)
+TRAFFIC_BYTES_PER_RAY = 2143.75e6 / 16777216  # profiles/r01_i_extend_ncu_full.txt: dram__bytes_read.sum 1880.8 MB + dram__bytes_write.sum 263.0 MB of one full 16 Mi-ray launch = 127.8 B/ray
 EXTEND_BYTES_PER_RAY = 128  # k_extend_persistent: reads 7 of the 8 path quads (ray, time, box-filter constants, ids: 112 B), writes one HitRef (16 B)
 
 
@@ -228,14 +228,14 @@ def run_ours(args):
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "spp_per_gpu": spp, "wave_paths": args.wave, "seed": args.seed, "rays_per_sample": rays / samples,
-                           "l2": "wavefront state per wave (>= 500 MB) exceeds the 126 MB L2; the scene (~100 kB) is meant to stay cached",
+                           "l2": "inputs larger than L2: the wavefront state streamed per wave (16 Mi paths x 128 B = 2 GB) exceeds the 126 MB L2; the scene (~100 kB) is meant to stay cached",
                            "parallelism": f"sample-range split x{world}, NCCL reduce of the fp64 accumulators" if world > 1 else "single GPU"},
                 "roofline": {"bound": "hbm", "kernel": "k_extend_persistent", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": TRAFFIC_BYTES_PER_LAUNCH, "peak_source": peak_src, "bytes_per_ray": EXTEND_BYTES_PER_RAY,
+                             "traffic": TRAFFIC_BYTES_PER_RAY * st["rays"] / max(1, st["waves"]), "peak_source": peak_src, "bytes_per_ray": EXTEND_BYTES_PER_RAY,
                              "extend_share_of_step": st["extend_ms"] / st["gpu_ms"],
                              "algorithmic_bytes_per_launch": st["rays"] * EXTEND_BYTES_PER_RAY / max(1, st["waves"]), "launches": st["waves"],
                              "note": "issue/latency bound, not HBM bound (fp32 box filter + binary64 reference-order leaf tests over an L1/L2-resident BVH); "
-                                     "traffic = dram read+write of one steady-state launch from profiles/ (ncu --set full); see DESIGN.md"},
+                                     "traffic = dram read+write per ray of a full launch from profiles/r01_i_extend_ncu_full.txt (ncu --set full) x mean rays per launch; see DESIGN.md"},
                 "e2e": e2e, "gpu_launches": int(launches * args.steps), "clocks": clocks}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()

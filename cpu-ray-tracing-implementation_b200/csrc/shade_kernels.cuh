@@ -5,9 +5,12 @@
 
 namespace b200 {
 
+#ifndef B200_SHADE_MINB
+#define B200_SHADE_MINB 8
+#endif
 // One launch per queue.  KIND = b200rt_material_kind of every hit in the queue, or B200_Q_MISS.
 template <int KIND, bool MIRROR>
-__global__ void __launch_bounds__(128) k_shade(WaveCtl *c, DevScene S, PathBuf cur, PathBuf nxt, const HitRef *hits, const Rec *recs,
+__global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevScene S, PathBuf cur, PathBuf nxt, const HitRef *hits, const Rec *recs,
                                                 const uint32_t *queue, double *accum, WaveParams wp) {
   // survivors are appended to the other pool with ONE global atomic per CTA iteration (same-address atomics are the
   // scarce resource of this kernel family: see k_classify); double-buffered by iteration parity
