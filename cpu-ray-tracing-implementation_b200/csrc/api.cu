@@ -8,6 +8,7 @@
 #include <mutex>
 
 #include "bvh_build.h"
+#include "bvh_gpu.cuh"
 #include "shade_kernels.cuh"
 
 using namespace b200;
@@ -63,6 +64,7 @@ struct b200rt_ctx {
   int extend_blocks = 4;
   int speculative = 0;
   int fuse_miss = 1;
+  int bvh_builder = B200RT_BVH_HOST_SAH;
   int extend_stages = 2; // 1 is within 1 % on RTOW / RTNW / Cornell and 11 % slower on Fox (profiles/r01_h_tune_l1.txt)
   int carveout_pct = -1; // -1 = computed from the kernel's footprint
   // scene
@@ -106,6 +108,81 @@ template <class T> int upload(b200rt_ctx *c, const T *src, size_t count, const T
     int rc_ = upload(c, src, (size_t)(count), dst, what);                                                              \
     if (rc_ != B200RT_OK) return rc_;                                                                                  \
   } while (0)
+
+// Device LBVH (bvh_gpu.cuh): leaves the finished nodes and the entries in leaf order in scene memory.
+int build_bvh_device(b200rt_ctx *c, const FlatScene &fs, DevScene &S, b200rt_bvh_info &info) {
+  const uint32_t n = (uint32_t)fs.boxes.size();
+  if (n >= (1u << 28)) return fail(B200RT_ERR_UNSUPPORTED, "device BVH build: %u primitives exceed the leaf reference range", n);
+  DevMem tmp;
+  cudaStream_t s = c->stream;
+  Box *d_boxes = nullptr;
+  Entry *d_in = nullptr, *d_out = nullptr;
+  uint32_t *codes[2] = {nullptr, nullptr}, *ids[2] = {nullptr, nullptr};
+  int2 *children = nullptr;
+  int *parent_inner = nullptr, *parent_leaf = nullptr;
+  unsigned int *arrived = nullptr;
+  Box32 *node_box = nullptr;
+  LbvhStats *st = nullptr;
+  BvhNode *nodes = nullptr;
+  const size_t ni = n > 1 ? n - 1 : 0;
+  CU(tmp.alloc((void **)&d_boxes, n * sizeof(Box)));
+  CU(tmp.alloc((void **)&d_in, n * sizeof(Entry)));
+  for (int k = 0; k < 2; k++) {
+    CU(tmp.alloc((void **)&codes[k], n * 4));
+    CU(tmp.alloc((void **)&ids[k], n * 4));
+  }
+  CU(tmp.alloc((void **)&children, ni * sizeof(int2)));
+  CU(tmp.alloc((void **)&parent_inner, ni * 4));
+  CU(tmp.alloc((void **)&parent_leaf, n * 4));
+  CU(tmp.alloc((void **)&arrived, ni * 4));
+  CU(tmp.alloc((void **)&node_box, ni * sizeof(Box32)));
+  CU(tmp.alloc((void **)&st, sizeof(LbvhStats)));
+  CU(c->scene_mem.alloc((void **)&nodes, ni * sizeof(BvhNode)));
+  CU(c->scene_mem.alloc((void **)&d_out, n * sizeof(Entry)));
+  size_t cub_bytes = 0;
+  CU(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, codes[0], codes[1], ids[0], ids[1], (int)n, 0, 30, s));
+  void *cub_tmp = nullptr;
+  CU(tmp.alloc(&cub_tmp, cub_bytes));
+  CU(cudaMemcpyAsync(d_boxes, fs.boxes.data(), n * sizeof(Box), cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(d_in, fs.entries.data(), n * sizeof(Entry), cudaMemcpyHostToDevice, s));
+  c->scene_h2d_bytes += (double)n * (sizeof(Box) + sizeof(Entry));
+  CU(cudaEventRecord(c->ev0, s));
+  const int g = (int)((n + 255) / 256);
+  k_lbvh_init<<<1, 1, 0, s>>>(st);
+  k_lbvh_bounds<<<std::min(g, c->sm_count * 8), 256, 0, s>>>(d_boxes, n, st);
+  k_lbvh_morton<<<g, 256, 0, s>>>(d_boxes, n, st, codes[0], ids[0]);
+  CU(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, codes[0], codes[1], ids[0], ids[1], (int)n, 0, 30, s));
+  CU(cudaMemsetAsync(parent_leaf, 0xFF, n * 4, s));
+  CU(cudaMemsetAsync(arrived, 0, ni * 4, s));
+  if (n > 1) k_lbvh_hierarchy<<<(int)((ni + 255) / 256), 256, 0, s>>>(codes[1], (int)n, children, parent_inner, parent_leaf);
+  k_lbvh_refit<<<g, 256, 0, s>>>(d_boxes, ids[1], (int)n, children, parent_inner, parent_leaf, arrived, node_box, nodes, st);
+  k_lbvh_gather<<<g, 256, 0, s>>>(d_in, ids[1], n, d_out);
+  CU(cudaEventRecord(c->ev1, s));
+  CU(cudaGetLastError());
+  LbvhStats h;
+  CU(cudaMemcpyAsync(&h, st, sizeof h, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+  S.bvh = nodes;
+  S.entries = d_out;
+  S.bvh_root = n > 1 ? 0 : ~0; // inner node 0 is the root of a Karras tree; a single primitive is a leaf reference
+  S.n_bvh_nodes = (uint32_t)ni;
+  S.n_entries = n;
+  for (int k = 0; k < 3; k++) {
+    float f;
+    std::memcpy(&f, &h.plane_max[k], 4);
+    S.bound[k] = (double)f;
+  }
+  info.n_nodes = (uint32_t)ni;
+  info.n_leaves = n;
+  info.n_prims = n;
+  info.max_depth = h.max_depth;
+  info.build_ms = ms;
+  info.sah_cost = h.root_area > 0 ? h.sah_acc / h.root_area : 0.0;
+  if (h.max_depth > B200_STACK) return fail(B200RT_ERR_UNSUPPORTED, "device BVH build: depth %u exceeds the traversal stack", h.max_depth);
+  return B200RT_OK;
+}
 
 int validate(const b200rt_scene_desc *d) {
   if (!d) return fail(B200RT_ERR_INVALID, "scene description is NULL");
@@ -220,6 +297,10 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
   case B200RT_OPT_EXTEND_BLOCKS: c->extend_blocks = (int)value; return B200RT_OK;
   case B200RT_OPT_SPECULATIVE_LEAF: c->speculative = value != 0; return B200RT_OK;
   case B200RT_OPT_FUSE_MISS: c->fuse_miss = value != 0; return B200RT_OK;
+  case B200RT_OPT_BVH_BUILDER:
+    if (value != B200RT_BVH_HOST_SAH && value != B200RT_BVH_DEVICE_LBVH) return fail(B200RT_ERR_INVALID, "BVH builder must be 0 (host SAH) or 1 (device LBVH)");
+    c->bvh_builder = (int)value; // takes effect at the next b200rt_upload_scene
+    return B200RT_OK;
   case B200RT_OPT_EXTEND_STAGES:
     if (value != 1 && value != 2) return fail(B200RT_ERR_INVALID, "extend stages must be 1 or 2");
     c->extend_stages = (int)value;
@@ -250,6 +331,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   FlatScene fs;
   BuiltBvh bvh;
   std::vector<Entry> ordered;
+  bool use_device_builder = false;
   try {
     Flattener fl(*d);
     fl.run();
@@ -266,9 +348,11 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
       if (mat < 0 || (uint32_t)mat >= d->n_materials)
         return fail(B200RT_ERR_UNSUPPORTED, "primitive %d has no material (the reference would dereference a null pointer)", e.prim);
     }
-    bvh = BvhBuilder(fs.boxes, c->bvh_leaf ? c->bvh_leaf : (fs.boxes.size() <= 8192 ? 1 : 2)).run();
-    ordered.resize(fs.entries.size());
-    for (size_t k = 0; k < ordered.size(); k++) ordered[k] = fs.entries[bvh.perm[k]];
+    if (!(use_device_builder = c->bvh_builder == B200RT_BVH_DEVICE_LBVH && !fs.boxes.empty())) {
+      bvh = BvhBuilder(fs.boxes, c->bvh_leaf ? c->bvh_leaf : (fs.boxes.size() <= 8192 ? 1 : 2)).run();
+      ordered.resize(fs.entries.size());
+      for (size_t k = 0; k < ordered.size(); k++) ordered[k] = fs.entries[bvh.perm[k]];
+    }
   } catch (const std::exception &e) {
     return fail(B200RT_ERR_INVALID, "scene description: %s", e.what());
   }
@@ -296,25 +380,34 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   S.light_kind = d->light_kind;
   S.light_index = d->light_index;
   S.background_tex = d->background_tex;
-  UP(bvh.nodes.data(), bvh.nodes.size(), &S.bvh, "bvh");
-  UP(ordered.data(), ordered.size(), &S.entries, "entries");
+  if (use_device_builder) {
+    rc = build_bvh_device(c, fs, S, c->bvh_info);
+    if (rc != B200RT_OK) return rc;
+  } else {
+    UP(bvh.nodes.data(), bvh.nodes.size(), &S.bvh, "bvh");
+    UP(ordered.data(), ordered.size(), &S.entries, "entries");
+  }
   UP(fs.bentries.data(), fs.bentries.size(), &S.bentries, "bentries");
   UP(fs.vol_inst.data(), fs.vol_inst.size(), &S.vol_inst, "vol_inst");
   UP(fs.chain_ops.data(), fs.chain_ops.size(), &S.chain_ops, "chain_ops");
   UP(fs.chains.data(), fs.chains.size(), &S.chains, "chains");
-  S.bvh_root = bvh.root;
-  S.n_bvh_nodes = (uint32_t)bvh.nodes.size();
-  S.n_entries = (uint32_t)ordered.size();
+  if (!use_device_builder) {
+    S.bvh_root = bvh.root;
+    S.n_bvh_nodes = (uint32_t)bvh.nodes.size();
+    S.n_entries = (uint32_t)ordered.size();
+    for (int k = 0; k < 3; k++) S.bound[k] = bvh.bound[k];
+  }
   S.has_volumes = fs.has_volumes ? 1 : 0;
-  for (int k = 0; k < 3; k++) S.bound[k] = bvh.bound[k];
   CU(cudaStreamSynchronize(c->stream)); // host vectors go out of scope
   c->S = S;
-  c->bvh_info.n_nodes = (uint32_t)bvh.nodes.size();
-  c->bvh_info.n_leaves = bvh.n_leaves;
-  c->bvh_info.n_prims = (uint32_t)ordered.size();
-  c->bvh_info.max_depth = bvh.max_depth;
-  c->bvh_info.build_ms = bvh.build_ms;
-  c->bvh_info.sah_cost = bvh.sah_cost;
+  if (!use_device_builder) {
+    c->bvh_info.n_nodes = (uint32_t)bvh.nodes.size();
+    c->bvh_info.n_leaves = bvh.n_leaves;
+    c->bvh_info.n_prims = (uint32_t)ordered.size();
+    c->bvh_info.max_depth = bvh.max_depth;
+    c->bvh_info.build_ms = bvh.build_ms;
+    c->bvh_info.sah_cost = bvh.sah_cost;
+  }
   c->graph_depth = fs.graph_depth;
   c->kinds_present = 0;
   for (uint32_t i = 0; i < d->n_materials; i++) c->kinds_present |= 1u << d->materials[i].kind;
@@ -562,9 +655,10 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
       // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
 #define EXT(MAXREG, SPEC, WARPS, STAGES)                                                                               \
   launch_extend(k_extend_persistent<MAXREG, SPEC, WARPS, STAGES>, c, 65536 / (MAXREG * WARPS * 32), WARPS * 32, WARPS * STAGES * 3584, s, cur, wp)
-      case 12: EXT(80, false, 4, 2); break;  // 24 warps per SM
-      case 10: EXT(96, false, 2, 2); break;  // 20 warps
-      case 18: EXT(112, false, 2, 2); break; // 18 warps (option value 9: 2-warp CTAs)
+      case 12: EXT(80, false, 4, 1); break;  // 24 warps per SM
+      case 10: EXT(96, false, 2, 1); break;  // 20 warps
+      case 18: EXT(112, false, 2, 1); break; // 18 warps (option value 9: 2-warp CTAs)
+      case 34: EXT(120, false, 1, 1); break; // 17 warps (option value 17: 1-warp CTAs)
       case 9: EXT(128, true, 4, 2); break;
       default:
         if (c->extend_stages == 1 && wp.refill == 32)

@@ -302,3 +302,56 @@ def test_sponza_standin_hits(ctx, build_oracle):
         assert same(got[k], ref[k]).all(), k
     img, st = ctx.render(3, 0, 2)
     assert np.isfinite(img).all() and st["rays"] > st["samples"]
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_device_built_bvh_gives_the_same_hits(name):
+    """B200RT_OPT_BVH_BUILDER = DEVICE_LBVH (csrc/bvh_gpu.cuh): a different tree, the same records as the reference."""
+    g = golden(name)
+    c = pkg.backend.Context(0)
+    try:
+        c.set_option(abi.OPT_BVH_BUILDER, abi.BVH_DEVICE_LBVH)
+        c.upload_scene(g.scene)
+        info = c.bvh_info()
+        assert info["n_leaves"] == info["n_prims"] and info["n_nodes"] == max(0, info["n_prims"] - 1)
+        assert 1 <= info["max_depth"] <= 64
+        out = c.trace(g["trace_rays"], seed=99)
+        ref = {k: g["trace_" + k] for k in ("prim", "t", "uv", "front", "p", "normal")}
+        keep = np.ones(len(out["prim"]), bool)
+        if name in VOLUME_SCENES:
+            vol = np.array(sorted(g.volume_prims()))
+            keep = ~np.isin(out["prim"], vol) & ~np.isin(ref["prim"], vol)
+        check_records(name, out, ref, keep)
+        # and the wavefront renders the same image from it (same samples, same hits; fp64 atomic order aside)
+        c.set_camera(g.cam_small)
+        img, st = c.render(5, 0, 4)
+        c.set_option(abi.OPT_BVH_BUILDER, abi.BVH_HOST_SAH)
+        c.upload_scene(g.scene)
+        img0, st0 = c.render(5, 0, 4)
+        assert st["rays"] == st0["rays"]
+        fin = np.isfinite(img0)
+        assert np.array_equal(fin, np.isfinite(img)) and np.allclose(img[fin], img0[fin], rtol=1e-12, atol=1e-12)
+    finally:
+        c.close()
+
+
+def test_device_built_bvh_sponza_standin():
+    sc = pkg.scene.sponza_standin_scene()
+    cam = pkg.camera.initialize_perspective(160, 16.0 / 9.0, (500, 320, 90), (0, 280, 0), 1, 45.0, 4, 5)
+    c = pkg.backend.Context(0)
+    try:
+        c.upload_scene(sc)
+        c.set_camera(cam)
+        rays = c.generate_rays(9, 0, 2)
+        host = c.trace(rays)
+        hinfo = c.bvh_info()
+        c.set_option(abi.OPT_BVH_BUILDER, abi.BVH_DEVICE_LBVH)
+        c.upload_scene(sc)
+        dev = c.trace(rays)
+        dinfo = c.bvh_info()
+        for k in ("prim", "front", "t", "p", "normal"):
+            assert same(host[k], dev[k]).all(), k
+        assert dinfo["n_prims"] == hinfo["n_prims"] and dinfo["build_ms"] < hinfo["build_ms"]
+        print(f"sponza stand-in BVH: host SAH {hinfo['build_ms']:.1f} ms (cost {hinfo['sah_cost']:.1f}), device LBVH {dinfo['build_ms']:.2f} ms (cost {dinfo['sah_cost']:.1f}, depth {dinfo['max_depth']})")
+    finally:
+        c.close()

@@ -45,9 +45,11 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="spp slice per scene (default: sized to ~0.5 G samples, at most the config's)")
     ap.add_argument("--scenes", default="cornell,rtow,rtnw,fox,sponza")
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--builder", type=int, default=0, help="0 = host SAH BVH (default), 1 = device LBVH (csrc/bvh_gpu.cuh)")
     ap.add_argument("--mirror", action="store_true", help="also time the node-for-node mirror traversal (parity arbiter)")
     args = ap.parse_args()
     ctx = pkg.backend.Context(0)
+    ctx.set_option(abi.OPT_BVH_BUILDER, args.builder)
     for name in args.scenes.split(","):
         t0 = time.perf_counter()
         sc, cam = load(name)
@@ -65,7 +67,7 @@ def main():
             _, st = ctx.render(1, 0, spp)
             if best is None or st["gpu_ms"] < best["gpu_ms"]:
                 best = st
-        line = {"scene": name, "config": CONFIGS[name], "width": cam.image_width, "height": cam.image_height, "spp_timed": spp,
+        line = {"scene": name, "builder": "device LBVH" if args.builder else "host SAH", "config": CONFIGS[name], "width": cam.image_width, "height": cam.image_height, "spp_timed": spp,
                 "spp_config": cam.samples_per_pixel, "max_depth": cam.max_depth, "mrays_per_s": best["rays"] / best["gpu_ms"] / 1e3,
                 "msamples_per_s": best["samples"] / best["gpu_ms"] / 1e3, "rays_per_sample": best["rays"] / best["samples"],
                 "gpu_ms": best["gpu_ms"], "extend_share": best["extend_ms"] / best["gpu_ms"], "waves": best["waves"],
