@@ -158,6 +158,8 @@ EXPORTS = [
     "b200rt_render",
     "b200rt_render_device",
     "b200rt_finalize",
+    "b200rt_ppm_bound",
+    "b200rt_format_ppm",
     "b200rt_bvh_info_get",
     "b200rt_texture_sample",
     "b200rt_abi_sizeof",
@@ -180,11 +182,14 @@ def bind(lib):
     lib.b200rt_render.argtypes = [vp, u64, i32, i32, vp, C.POINTER(Stats)]
     lib.b200rt_render_device.argtypes = [vp, u64, i32, i32, vp, vp, C.POINTER(Stats)]
     lib.b200rt_finalize.argtypes = [vp, vp, i32, vp, vp]
+    lib.b200rt_ppm_bound.argtypes = [i32, i32]
+    lib.b200rt_format_ppm.argtypes = [vp, vp, i32, vp, sz, C.POINTER(sz)]
     lib.b200rt_bvh_info_get.argtypes = [vp, C.POINTER(BvhInfo)]
     lib.b200rt_texture_sample.argtypes = [vp, i32, vp, sz, vp]
     lib.b200rt_abi_sizeof.argtypes = [i32]
     for name in EXPORTS:
-        if name not in ("b200rt_last_error", "b200rt_abi_sizeof"):
+        if name not in ("b200rt_last_error", "b200rt_abi_sizeof", "b200rt_ppm_bound"):
             getattr(lib, name).restype = C.c_int
     lib.b200rt_abi_sizeof.restype = C.c_size_t
+    lib.b200rt_ppm_bound.restype = C.c_size_t
     return lib

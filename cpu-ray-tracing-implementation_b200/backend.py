@@ -132,3 +132,13 @@ class Context:
         ppm = np.zeros(rgb_sum.shape, np.int32) if want_ppm else None
         self._check(self._lib.b200rt_finalize(self._h, rgb_sum.ctypes.data, total_spp, lin.ctypes.data, _ptr(ppm)))
         return (lin, ppm) if want_ppm else lin
+
+    def format_ppm(self, rgb_sum, total_spp, capacity=None):
+        """The complete P3 file image camera::render would write (src/camera.h:149-151, 174), as bytes; text made on the device."""
+        rgb_sum = np.ascontiguousarray(rgb_sum, dtype=np.float64)
+        cap = int(capacity if capacity is not None else self._lib.b200rt_ppm_bound(self.camera.image_width, self.camera.image_height))
+        buf = np.empty(max(cap, 1), np.uint8)
+        n = C.c_size_t(0)
+        self._check(self._lib.b200rt_format_ppm(self._h, rgb_sum.ctypes.data, total_spp, buf.ctypes.data, cap, C.byref(n)))
+        return buf[: n.value].tobytes()
+

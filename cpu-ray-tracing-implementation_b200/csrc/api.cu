@@ -9,6 +9,7 @@
 
 #include "bvh_build.h"
 #include "bvh_gpu.cuh"
+#include "output.cuh"
 #include "shade_kernels.cuh"
 
 using namespace b200;
@@ -755,6 +756,49 @@ int b200rt_finalize(b200rt_ctx *c, const double *rgb_sum, int total_spp, double 
   if (rgb_linear) CU(cudaMemcpyAsync(rgb_linear, d_lin, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   if (ppm_rgb) CU(cudaMemcpyAsync(ppm_rgb, d_ppm, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
+  return B200RT_OK;
+}
+
+size_t b200rt_ppm_bound(int image_width, int image_height) {
+  if (image_width <= 0 || image_height <= 0) return 0;
+  return 64 + (size_t)image_width * (size_t)image_height * 36; // header + three 11-character integers, two blanks and a newline per pixel
+}
+
+int b200rt_format_ppm(b200rt_ctx *c, const double *rgb_sum, int total_spp, char *out, size_t capacity, size_t *out_len) {
+  if (!c || !rgb_sum || !out || !out_len) return fail(B200RT_ERR_INVALID, "NULL argument");
+  if (!c->have_camera) return fail(B200RT_ERR_STATE, "format_ppm before b200rt_set_camera");
+  if (total_spp <= 0) return fail(B200RT_ERR_INVALID, "total_spp must be positive");
+  CU(cudaSetDevice(c->device));
+  const size_t npix = (size_t)c->cam.image_width * c->cam.image_height;
+  char header[64];
+  const int hl = snprintf(header, sizeof header, "P3\n%d %d\n255\n", c->cam.image_width, c->cam.image_height); // src/camera.h:149-151
+  const size_t bound = b200rt_ppm_bound(c->cam.image_width, c->cam.image_height);
+  const size_t dev_cap = capacity < bound ? capacity : bound;
+  if (dev_cap < (size_t)hl) return fail(B200RT_ERR_INVALID, "format_ppm: capacity %zu is smaller than the header", capacity);
+  const uint32_t n_cta = (uint32_t)((npix + B200_PPM_CTA * B200_PPM_PER_THREAD - 1) / (B200_PPM_CTA * B200_PPM_PER_THREAD));
+  DevMem tmp;
+  double *d_sum = nullptr;
+  int32_t *d_rgb = nullptr;
+  unsigned long long *d_cta = nullptr, *d_total = nullptr;
+  char *d_out = nullptr;
+  CU(tmp.alloc((void **)&d_sum, npix * 3 * sizeof(double)));
+  CU(tmp.alloc((void **)&d_rgb, npix * 3 * sizeof(int32_t)));
+  CU(tmp.alloc((void **)&d_cta, (size_t)n_cta * 8));
+  CU(tmp.alloc((void **)&d_total, 8));
+  CU(tmp.alloc((void **)&d_out, dev_cap));
+  CU(cudaMemcpyAsync(d_sum, rgb_sum, npix * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_ppm_measure<<<n_cta, B200_PPM_CTA, 0, c->stream>>>(d_sum, npix, (double)total_spp, d_rgb, d_cta);
+  k_ppm_scan<<<1, B200_PPM_CTA, 0, c->stream>>>(d_cta, n_cta, (unsigned long long)hl, d_total);
+  k_ppm_write<<<n_cta, B200_PPM_CTA, 0, c->stream>>>(d_rgb, npix, d_cta, d_out, dev_cap);
+  CU(cudaGetLastError());
+  unsigned long long total = 0;
+  CU(cudaMemcpyAsync(&total, d_total, 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  *out_len = (size_t)total;
+  if (total > capacity) return fail(B200RT_ERR_INVALID, "format_ppm: the file needs %llu bytes, capacity is %zu (b200rt_ppm_bound() always suffices)", total, capacity);
+  CU(cudaMemcpyAsync(out + hl, d_out + hl, (size_t)total - hl, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  std::memcpy(out, header, hl);
   return B200RT_OK;
 }
 

@@ -292,6 +292,14 @@ int b200rt_render_device(b200rt_ctx *ctx, uint64_t seed, int spp_begin, int spp_
  * rgb_linear = rgb_sum / total_spp (may alias); ppm_rgb (may be NULL) gets int(255.999 * pow(c, 1/2.2)), unclamped. */
 int b200rt_finalize(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, double *rgb_linear, int32_t *ppm_rgb);
 
+/* Replaces the output stage of camera::render: the "P3\nW H\n255\n" header (src/camera.h:149-151) and the
+ * std::for_each(image_, write_color) loop (src/camera.h:174, src/color.h:22-36).  `out` receives the complete file image
+ * exactly as the reference's ofstream would hold it (one "r g b\n" line per pixel, integers unclamped, no terminator);
+ * *out_len = its length.  The integer-to-text conversion runs on the device.  A `capacity` of
+ * b200rt_ppm_bound(W, H) always suffices; a smaller one fails with B200RT_ERR_INVALID and *out_len = the size needed. */
+size_t b200rt_ppm_bound(int image_width, int image_height);
+int b200rt_format_ppm(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, char *out, size_t capacity, size_t *out_len);
+
 /* Replaces: texture::sample(u, v, p) (src/texture.h:9) of texture row `tex` on a batch.
  * uvp5 = n x {u, v, p[3]}, rgb = n x 3.  Host buffers. */
 int b200rt_texture_sample(b200rt_ctx *ctx, int tex, const double *uvp5, size_t n, double *rgb);

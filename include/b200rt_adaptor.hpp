@@ -478,14 +478,15 @@ inline void render(camera &cam, std::ofstream &out, const hittable &world, const
   check(b200rt_set_camera(ctx, &cd));
   std::vector<double> sum((size_t)cd.image_width * cd.image_height * 3);
   check(b200rt_render(ctx, seed, 0, cd.samples_per_pixel, sum.data(), nullptr));
+  // output stage on the device: the header and one write_color line per pixel (src/camera.h:149-151, 174; src/color.h:22-36)
+  std::vector<char> text(b200rt_ppm_bound(cd.image_width, cd.image_height));
+  size_t text_len = 0;
+  check(b200rt_format_ppm(ctx, sum.data(), cd.samples_per_pixel, text.data(), text.size(), &text_len));
   check(b200rt_finalize(ctx, sum.data(), cd.samples_per_pixel, sum.data(), nullptr));
   b200rt_destroy(ctx);
-  out << "P3\n" << cd.image_width << ' ' << cd.image_height << "\n255\n";
-  cam.image_.resize((size_t)cd.image_width * cd.image_height);
-  for (size_t i = 0; i < cam.image_.size(); i++) {
-    cam.image_[i] = color(sum[3 * i], sum[3 * i + 1], sum[3 * i + 2]);
-    write_color(out, cam.image_[i]); // the reference's own output stage, src/color.h:22-36
-  }
+  out.write(text.data(), (std::streamsize)text_len);
+  cam.image_.resize((size_t)cd.image_width * cd.image_height); // pixel_color / spp, as camera::render leaves it (src/camera.h:169-170)
+  for (size_t i = 0; i < cam.image_.size(); i++) cam.image_[i] = color(sum[3 * i], sum[3 * i + 1], sum[3 * i + 2]);
 }
 #endif
 

@@ -66,7 +66,19 @@
 #include "volumne.h"
 #undef private
 
-#define B200RT_ADAPTOR_NO_RENDER
+// The adaptor's b200::render (the drop-in for camera::render) is compiled here too, so that the test suite can drive the
+// whole reference-side binding: reference objects -> adaptor -> C ABI -> GPU -> P3 file.  Its b200rt_* calls are weak: this
+// checker library must load (and serve the oracle tests) where libb200rt.so is not loaded; ref_render_b200 reports that.
+#include "b200rt.h"
+#pragma weak b200rt_create
+#pragma weak b200rt_destroy
+#pragma weak b200rt_last_error
+#pragma weak b200rt_upload_scene
+#pragma weak b200rt_set_camera
+#pragma weak b200rt_render
+#pragma weak b200rt_finalize
+#pragma weak b200rt_ppm_bound
+#pragma weak b200rt_format_ppm
 #include "b200rt_adaptor.hpp"
 
 // ------------------------------------------------------------------------------------------------
@@ -822,6 +834,34 @@ double ref_render_stock(int h, unsigned seed, int spp, const char *ppm_path, dou
   if (rgb_linear)
     for (size_t i = 0; i < cam.image_.size(); i++)
       for (int k = 0; k < 3; k++) rgb_linear[3 * i + k] = cam.image_[i].e[k];
+  return secs;
+}
+
+// b200::render(cam, out, world, light) — the binding of INTEGRATION.md — in place of cam.render(out, world, light).
+// Needs libb200rt.so loaded with RTLD_GLOBAL before this library.  Returns wall seconds, < 0 on error (ref_last_error()).
+double ref_render_b200(int h, unsigned long long seed, int spp, int device, const char *ppm_path, double *rgb_linear) {
+  scene *s = get(h);
+  if (!s) return -1.0;
+  if (!b200rt_create || !b200rt_format_ppm) {
+    t_err = "libb200rt.so is not loaded (load it with RTLD_GLOBAL first)";
+    return -2.0;
+  }
+  camera &cam = s->cam;
+  int keep = cam.samples_per_pixel_;
+  if (spp > 0) cam.samples_per_pixel_ = spp;
+  std::ofstream out(ppm_path ? ppm_path : "/dev/null");
+  double secs = -3.0;
+  try {
+    auto t0 = std::chrono::steady_clock::now();
+    b200::render(cam, out, *s->world, s->light, device, seed);
+    secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (rgb_linear)
+      for (size_t i = 0; i < cam.image_.size(); i++)
+        for (int k = 0; k < 3; k++) rgb_linear[3 * i + k] = cam.image_[i].e[k];
+  } catch (const std::exception &e) {
+    t_err = e.what();
+  }
+  cam.samples_per_pixel_ = keep;
   return secs;
 }
 

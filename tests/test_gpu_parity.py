@@ -256,6 +256,28 @@ def test_finalize_matches_write_color(ctx):
     assert (np.abs(ppm.astype(np.int64) - ref) <= 1).all() and (ppm[big] == -(2**31)).all()
 
 
+def test_format_ppm_is_the_reference_file_image(ctx):
+    """b200rt_format_ppm == header + one `out << r << ' ' << g << ' ' << b << '\\n'` per pixel (src/camera.h:149-151, src/color.h:35),
+    with the integers of b200rt_finalize: negative, > 255 and INT_MIN values print like operator<<(int)."""
+    g = golden("cornell")
+    for W, H in ((37, 29), (64, 33), (1, 1), (1030, 3)):
+        cam = g.cam_small.copy()
+        cam.image_width, cam.image_height = W, H
+        ctx.set_camera(cam)
+        rng = np.random.RandomState(W)
+        s = rng.rand(H, W, 3) * 10 ** rng.uniform(-3, 3, size=(H, W, 3))
+        s.reshape(-1)[:3] = [np.nan, -3.0, 1e300]
+        s.reshape(-1)[-1] = 0.0
+        _, ppm = ctx.finalize(s, 16, want_ppm=True)
+        want = f"P3\n{W} {H}\n255\n" + "".join(f"{r} {gg} {b}\n" for r, gg, b in ppm.reshape(-1, 3).tolist())
+        got = ctx.format_ppm(s, 16)
+        assert got == want.encode()
+        with pytest.raises(pkg.backend.B200RTError):
+            ctx.format_ppm(s, 16, capacity=len(want) - 1)
+        assert ctx.format_ppm(s, 16, capacity=len(want)) == want.encode()
+    ctx.set_camera(g.cam_small)
+
+
 def test_errors_are_loud(ctx):
     from conftest import Scene
 
@@ -355,3 +377,33 @@ def test_device_built_bvh_sponza_standin():
         print(f"sponza stand-in BVH: host SAH {hinfo['build_ms']:.1f} ms (cost {hinfo['sah_cost']:.1f}), device LBVH {dinfo['build_ms']:.2f} ms (cost {dinfo['sah_cost']:.1f}, depth {dinfo['max_depth']})")
     finally:
         c.close()
+
+
+@pytest.mark.parametrize("name", ["cornell", "rtow", "three_ball_lens"])
+def test_reference_side_binding_end_to_end(name, tmp_path):
+    """INTEGRATION.md's drop-in: b200::render(cam, out, world, light) of include/b200rt_adaptor.hpp, compiled against the
+    UNMODIFIED reference headers (oracle/_ref), called on live reference objects in place of cam.render(...): the P3 file
+    it writes and the cam.image_ it leaves equal what the C ABI gives for the flattened scene on the same Philox seed."""
+    import refharness
+
+    if not refharness.available():
+        pytest.skip("oracle/_ref/libref_harness.so not built (needs /root/reference at build time)")
+    rs = refharness.RefScene(name, width=56, spp=5, depth=12)
+    path = str(tmp_path / "b200.ppm")
+    secs, img = rs.render_b200(seed=0x5EED, ppm_path=path)
+    text = open(path, "rb").read()
+    H, W = rs.camera.image_height, rs.camera.image_width
+    assert text.startswith(f"P3\n{W} {H}\n255\n".encode())
+    with pkg.backend.Context(0) as c:
+        c.upload_scene(rs.scene)
+        c.set_camera(rs.camera)
+        s, _ = c.render(0x5EED, 0, rs.camera.samples_per_pixel)
+        lin = c.finalize(s, rs.camera.samples_per_pixel)
+        want = c.format_ppm(s, rs.camera.samples_per_pixel)
+    fin = np.isfinite(lin)
+    assert np.allclose(img[fin], lin[fin], rtol=1e-12, atol=1e-12)
+    got_ints = np.array(text.split()[4:], dtype=np.int64)
+    want_ints = np.array(want.split()[4:], dtype=np.int64)
+    assert got_ints.shape == want_ints.shape == (H * W * 3,)
+    assert (np.abs(got_ints - want_ints) <= 1).all() and (got_ints != want_ints).mean() < 1e-3  # fp64 atomic order can move a value across an integer boundary
+    rs.close()
