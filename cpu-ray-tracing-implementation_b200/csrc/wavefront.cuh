@@ -40,7 +40,22 @@ struct PathBuf {
   double2 *base;
   uint32_t capacity;
 };
-DEV const double2 *quad_ptr(const PathBuf &b, int q, uint32_t i) { return b.base + (size_t)q * b.capacity + i; }
+// Column layout (default): quad q of path i at q * capacity + i.  B200_PATH_PAIRED=1 stores quads 2k and 2k+1 of one path in
+// one 32-byte sector, so that the queue-ordered gathers of the shade kernels (q0 q1 q2 q3 q6 q7) fetch three full sectors
+// per path instead of six half-used ones.  Measured on B200 (profiles/r01_k_layout.txt): the gathers get cheaper, but every
+// coalesced pass (generate, extend staging, compacted stores) then moves 16 bytes per lane at a 32-byte stride, and the
+// frame is 4.5 % SLOWER (RTOW 5.34 vs 5.60 Grays/s).  Kept as a compile-time experiment only.
+#ifndef B200_PATH_PAIRED
+#define B200_PATH_PAIRED 0
+#endif
+DEV size_t quad_index(uint32_t capacity, int q, uint32_t i) {
+#if B200_PATH_PAIRED
+  return ((size_t)(q >> 1) * capacity + i) * 2 + (size_t)(q & 1);
+#else
+  return (size_t)q * capacity + i;
+#endif
+}
+DEV const double2 *quad_ptr(const PathBuf &b, int q, uint32_t i) { return b.base + quad_index(b.capacity, q, i); }
 
 struct WaveParams {
   uint64_t seed;
@@ -77,16 +92,16 @@ DEV RaySetup load_setup(const PathBuf &b, uint32_t i, const Ray &r) {
   return s;
 }
 DEV void store_path(const PathBuf &b, uint32_t i, const Ray &r, const V &T, uint32_t pixel, uint32_t sample, uint32_t bounce, const RaySetup &s) {
-  double2 *q = b.base + i;
-  const size_t n = b.capacity;
-  q[0] = make_double2(r.o.x, r.o.y);
-  q[n] = make_double2(r.o.z, r.d.x);
-  q[2 * n] = make_double2(r.d.y, r.d.z);
-  q[3 * n] = make_double2(r.tm, T.x);
-  *reinterpret_cast<float4 *>(q + 4 * n) = make_float4(s.ix, s.iy, s.iz, s.c0x);
-  *reinterpret_cast<float4 *>(q + 5 * n) = make_float4(s.c1x, s.c0y, s.c1y, s.c0z);
-  *reinterpret_cast<float4 *>(q + 6 * n) = make_float4(s.c1z, __uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(bounce));
-  q[7 * n] = make_double2(T.y, T.z);
+  double2 *q = b.base;
+  const uint32_t n = b.capacity;
+  q[quad_index(n, 0, i)] = make_double2(r.o.x, r.o.y);
+  q[quad_index(n, 1, i)] = make_double2(r.o.z, r.d.x);
+  q[quad_index(n, 2, i)] = make_double2(r.d.y, r.d.z);
+  q[quad_index(n, 3, i)] = make_double2(r.tm, T.x);
+  *reinterpret_cast<float4 *>(q + quad_index(n, 4, i)) = make_float4(s.ix, s.iy, s.iz, s.c0x);
+  *reinterpret_cast<float4 *>(q + quad_index(n, 5, i)) = make_float4(s.c1x, s.c0y, s.c1y, s.c0z);
+  *reinterpret_cast<float4 *>(q + quad_index(n, 6, i)) = make_float4(s.c1z, __uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(bounce));
+  q[quad_index(n, 7, i)] = make_double2(T.y, T.z);
 }
 
 // warp-aggregated append: one atomic per warp per queue; must be reached by all 32 lanes
