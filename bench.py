@@ -107,7 +107,7 @@ def run_reference(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    spp_step = 1
+    spp_step = 4
     for _ in range(args.warmup):
         cpu_reference_run(1200, spp_step, threads)
     tot_s = tot_r = 0

@@ -40,11 +40,37 @@ def load(name):
     return pkg.scene.Scene.load(z), abi.Camera.from_bytes(z["camera"].tobytes())
 
 
+def cpu_baseline(name, sc, cam):
+    """The reference's CPU code on this box's host threads, beside the GPU number (a reported baseline, not a target).
+    cornell / rtow: the reference itself (oracle/_ref: its own ray_color / generate_ray on objects built by its constructors).
+    rtnw / fox / sponza need assets that only exist next to the reference checkout, so there the oracle port (oracle/oracle.cc,
+    same algorithm on the flattened scene, same reference-order tree) is timed instead; sponza at 480x270 (its x-sorted
+    reference tree costs about a millisecond per ray on one core)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracleport
+    import refharness
+
+    threads = os.cpu_count() or 1
+    if name in ("cornell", "rtow") and refharness.available():
+        rs = refharness.RefScene(name, width=cam.image_width, spp=cam.samples_per_pixel, depth=cam.max_depth)
+        _, _, st = rs.render(2, seed=12345, threads=threads, rng_mode=1, want_sums=False)
+        rs.close()
+        return {"kind": "reference", "cores": st["threads"], "mrays_per_s": st["rays"] / st["seconds"] / 1e6, "msamples_per_s": st["samples"] / st["seconds"] / 1e6,
+                "sample": f"{cam.image_width}x{cam.image_height} at 2 spp in {st['seconds']:.2f} s"}
+    if name == "sponza":
+        cam = pkg.camera.initialize_perspective(480, 16.0 / 9.0, (500, 320, 90), (0, 280, 0), 1, 45.0, 1, 5)
+    r = oracleport.render(sc, cam, 12345, 0, 1, threads=threads)
+    st = r["stats"]
+    return {"kind": "port", "cores": threads, "mrays_per_s": st["rays"] / st["seconds"] / 1e6, "msamples_per_s": st["samples"] / st["seconds"] / 1e6,
+            "sample": f"{cam.image_width}x{cam.image_height} at 1 spp in {st['seconds']:.2f} s"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--spp", type=int, default=0, help="spp slice per scene (default: sized to ~0.5 G samples, at most the config's)")
     ap.add_argument("--scenes", default="cornell,rtow,rtnw,fox,sponza")
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--cpu", action="store_true", help="add the CPU baseline of every scene (see cpu_baseline)")
     ap.add_argument("--builder", type=int, default=0, help="0 = host SAH BVH (default), 1 = device LBVH (csrc/bvh_gpu.cuh)")
     ap.add_argument("--mirror", action="store_true", help="also time the node-for-node mirror traversal (parity arbiter)")
     args = ap.parse_args()
@@ -80,6 +106,8 @@ def main():
             _, sm = ctx.render(1, 0, max(1, spp // 16))
             ctx.set_option(abi.OPT_TRAVERSAL, abi.TRAVERSAL_FAST)
             line["mirror_mrays_per_s"] = sm["rays"] / sm["gpu_ms"] / 1e3
+        if args.cpu:
+            line["cpu_baseline"] = cpu_baseline(name, sc, cam)
         print(json.dumps(line), flush=True)
     ctx.close()
 
