@@ -5,6 +5,19 @@
 
 namespace b200 {
 
+// The shade kernels are chains of dependent gathers (queue index -> path columns + hit reference -> entry -> primitive ->
+// material -> texture) at 32 warps per SM.  Experiment (-DB200_SHADE_PREFETCH=1): while a CTA works on one 128-path slice,
+// every thread asks L2 (prefetch.global.L2) for the seven sectors its NEXT slice will gather.  Measured on B200: 5 % SLOWER
+// on RTOW (5.34 vs 5.60 Grays/s, profiles/r01_k_layout.txt) - the kernels are limited by memory requests in flight, not by
+// the latency of each, and the prefetches are extra requests.  Off.
+#ifndef B200_SHADE_PREFETCH
+#define B200_SHADE_PREFETCH 0
+#endif
+DEV void prefetch_l2(const void *p) {
+#ifndef B200_HOST_EMU
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#endif
+}
 #ifndef B200_SHADE_MINB
 #define B200_SHADE_MINB 8
 #endif
@@ -20,6 +33,17 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
   int par = 0;
   for (uint32_t bbase = blockIdx.x * 128; bbase < n; bbase += gridDim.x * 128, par ^= 1) {
     const uint32_t j = bbase + threadIdx.x;
+#if B200_SHADE_PREFETCH
+    {
+      const uint32_t jn = j + gridDim.x * 128;
+      if (jn < n) {
+        const uint32_t in = queue[jn];
+        prefetch_l2(quad_ptr(cur, 0, in)), prefetch_l2(quad_ptr(cur, 1, in)), prefetch_l2(quad_ptr(cur, 2, in)), prefetch_l2(quad_ptr(cur, 3, in));
+        prefetch_l2(quad_ptr(cur, 6, in)), prefetch_l2(quad_ptr(cur, 7, in));
+        if (KIND != B200_Q_MISS && !MIRROR) prefetch_l2(hits + in);
+      }
+    }
+#endif
     bool survives = false;
     Ray out_ray;
     V T;
