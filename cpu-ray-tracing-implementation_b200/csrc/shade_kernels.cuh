@@ -50,9 +50,8 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
     uint32_t pixel = 0, sample = 0, bounce = 0;
     if (j < n) {
       const uint32_t i = queue[j];
-      const PathHead ph = load_head(cur, i);
+      const PathHead ph = load_head(cur, i, &T);
       const Ray r = ph.r;
-      T = load_throughput(cur, i);
       pixel = ph.pixel;
       sample = ph.sample;
       bounce = ph.bounce;

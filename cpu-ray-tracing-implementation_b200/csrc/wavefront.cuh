@@ -40,13 +40,13 @@ struct PathBuf {
   double2 *base;
   uint32_t capacity;
 };
-// Column layout (default): quad q of path i at q * capacity + i.  B200_PATH_PAIRED=1 stores quads 2k and 2k+1 of one path in
-// one 32-byte sector, so that the queue-ordered gathers of the shade kernels (q0 q1 q2 q3 q6 q7) fetch three full sectors
-// per path instead of six half-used ones.  Measured on B200 (profiles/r01_k_layout.txt): the gathers get cheaper, but every
-// coalesced pass (generate, extend staging, compacted stores) then moves 16 bytes per lane at a 32-byte stride, and the
-// frame is 4.5 % SLOWER (RTOW 5.34 vs 5.60 Grays/s).  Kept as a compile-time experiment only.
+// B200_PATH_PAIRED=0: quad q of path i at q * capacity + i (eight columns of 16 bytes).
+// B200_PATH_PAIRED=1: quads 2k and 2k+1 of one path share a 32-byte sector (four columns of 32 bytes) and are moved by ONE
+// 256-bit access (LDG/STG.E.ENL2.256 on sm_100a): the queue-ordered gathers of the shade kernels read q0..q3, q6, q7 as three
+// full sectors with three requests instead of six half-used sectors with six; producers write four 32-byte stores per path.
+// (Pairing WITHOUT the 256-bit accesses was measured 4.5 % slower than columns: 16 bytes per lane at a 32-byte stride.)
 #ifndef B200_PATH_PAIRED
-#define B200_PATH_PAIRED 0
+#define B200_PATH_PAIRED 1
 #endif
 DEV size_t quad_index(uint32_t capacity, int q, uint32_t i) {
 #if B200_PATH_PAIRED
@@ -69,31 +69,50 @@ struct PathHead { // what every consumer needs
   Ray r;
   uint32_t pixel, sample, bounce;
 };
-DEV PathHead load_head(const PathBuf &b, uint32_t i) {
+#if B200_PATH_PAIRED
+// one 256-bit access = two adjacent quads; p must be 32-byte aligned
+DEV void ld256(const double2 *p, double2 &a, double2 &b) {
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a.x), "=d"(a.y), "=d"(b.x), "=d"(b.y) : "l"(p));
+}
+DEV void st256(double2 *p, const double2 &a, const double2 &b) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a.x), "d"(a.y), "d"(b.x), "d"(b.y) : "memory");
+}
+DEV double pack2(float lo, float hi) { return __hiloint2double(__float_as_int(hi), __float_as_int(lo)); }
+DEV float unpack_lo(double d) { return __int_as_float(__double2loint(d)); }
+DEV float unpack_hi(double d) { return __int_as_float(__double2hiint(d)); }
+#endif
+// ray, ids and throughput of path i: everything a shade kernel gathers
+DEV PathHead load_head(const PathBuf &b, uint32_t i, V *T = nullptr) {
+  PathHead h;
+#if B200_PATH_PAIRED
+  double2 q0, q1, q2, q3, q6, q7;
+  ld256(quad_ptr(b, 0, i), q0, q1);
+  ld256(quad_ptr(b, 2, i), q2, q3);
+  ld256(quad_ptr(b, 6, i), q6, q7);
+  h.r = Ray{v3(q0.x, q0.y, q1.x), v3(q1.y, q2.x, q2.y), q3.x};
+  h.pixel = (uint32_t)__double2hiint(q6.x), h.sample = (uint32_t)__double2loint(q6.y), h.bounce = (uint32_t)__double2hiint(q6.y);
+  if (T) *T = v3(q3.y, q7.x, q7.y);
+#else
   const double2 q0 = __ldg(quad_ptr(b, 0, i)), q1 = __ldg(quad_ptr(b, 1, i)), q2 = __ldg(quad_ptr(b, 2, i)), q3 = __ldg(quad_ptr(b, 3, i));
   const int4 q6 = __ldg(reinterpret_cast<const int4 *>(quad_ptr(b, 6, i)));
-  PathHead h;
   h.r = Ray{v3(q0.x, q0.y, q1.x), v3(q1.y, q2.x, q2.y), q3.x};
   h.pixel = (uint32_t)q6.y, h.sample = (uint32_t)q6.z, h.bounce = (uint32_t)q6.w;
+  if (T) {
+    const double2 q7 = __ldg(quad_ptr(b, 7, i));
+    *T = v3(q3.y, q7.x, q7.y);
+  }
+#endif
   return h;
-}
-DEV V load_throughput(const PathBuf &b, uint32_t i) {
-  const double2 q3 = __ldg(quad_ptr(b, 3, i)), q7 = __ldg(quad_ptr(b, 7, i));
-  return v3(q3.y, q7.x, q7.y);
-}
-DEV RaySetup load_setup(const PathBuf &b, uint32_t i, const Ray &r) {
-  const float4 q4 = __ldg(reinterpret_cast<const float4 *>(quad_ptr(b, 4, i))), q5 = __ldg(reinterpret_cast<const float4 *>(quad_ptr(b, 5, i)));
-  const float4 q6 = __ldg(reinterpret_cast<const float4 *>(quad_ptr(b, 6, i)));
-  RaySetup s;
-  s.ix = q4.x, s.iy = q4.y, s.iz = q4.z, s.c0x = q4.w;
-  s.c1x = q5.x, s.c0y = q5.y, s.c1y = q5.z, s.c0z = q5.w;
-  s.c1z = q6.x;
-  s.tsc = ray_tsc(r.d);
-  return s;
 }
 DEV void store_path(const PathBuf &b, uint32_t i, const Ray &r, const V &T, uint32_t pixel, uint32_t sample, uint32_t bounce, const RaySetup &s) {
   double2 *q = b.base;
   const uint32_t n = b.capacity;
+#if B200_PATH_PAIRED
+  st256(q + quad_index(n, 0, i), make_double2(r.o.x, r.o.y), make_double2(r.o.z, r.d.x));
+  st256(q + quad_index(n, 2, i), make_double2(r.d.y, r.d.z), make_double2(r.tm, T.x));
+  st256(q + quad_index(n, 4, i), make_double2(pack2(s.ix, s.iy), pack2(s.iz, s.c0x)), make_double2(pack2(s.c1x, s.c0y), pack2(s.c1y, s.c0z)));
+  st256(q + quad_index(n, 6, i), make_double2(pack2(s.c1z, __uint_as_float(pixel)), pack2(__uint_as_float(sample), __uint_as_float(bounce))), make_double2(T.y, T.z));
+#else
   q[quad_index(n, 0, i)] = make_double2(r.o.x, r.o.y);
   q[quad_index(n, 1, i)] = make_double2(r.o.z, r.d.x);
   q[quad_index(n, 2, i)] = make_double2(r.d.y, r.d.z);
@@ -102,6 +121,7 @@ DEV void store_path(const PathBuf &b, uint32_t i, const Ray &r, const V &T, uint
   *reinterpret_cast<float4 *>(q + quad_index(n, 5, i)) = make_float4(s.c1x, s.c0y, s.c1y, s.c0z);
   *reinterpret_cast<float4 *>(q + quad_index(n, 6, i)) = make_float4(s.c1z, __uint_as_float(pixel), __uint_as_float(sample), __uint_as_float(bounce));
   q[quad_index(n, 7, i)] = make_double2(T.y, T.z);
+#endif
 }
 
 // warp-aggregated append: one atomic per warp per queue; must be reached by all 32 lanes
@@ -281,7 +301,11 @@ DEV void cp_async_wait_all() {
 // smaller footprint (14 KB instead of 28 KB per CTA) is not free to give away: see DESIGN.md.
 template <int MAXREG, bool SPEC, int WARPS, int STAGES>
 __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp) {
+#if B200_PATH_PAIRED
+  __shared__ __align__(32) double2 stage_mem[WARPS][STAGES][224]; // warp x stage x {3 columns x 32 paths x 2 quads, then q6 of 32 paths}: 3.5 KB
+#else
   __shared__ __align__(16) double2 stage_mem[WARPS][STAGES][B200_EXT_QUADS][32]; // warp x stage x quad x lane: 3.5 KB per warp and stage
+#endif
   const uint32_t n = c->n_cur;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const unsigned FULL = 0xffffffffu;
@@ -289,11 +313,26 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
   const int refill = wp.refill, keep = 33 - wp.refill;
 
   auto prefetch = [&](int stg, uint32_t batch) { // one cp.async group per call, also when there is nothing to copy
+#if B200_PATH_PAIRED
+    // a batch is 1 KB contiguous per 32-byte column: lane l copies 16-byte chunks l and 32 + l of each (fully coalesced)
+    if (batch < n_batches) {
+      const uint32_t i0 = batch * 32;
+#pragma unroll
+      for (int c = 0; c < 3; c++)
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+          const uint32_t ch = 32 * k + lane;
+          if (i0 + (ch >> 1) < n) cp_async16(&stage_mem[wib][stg][64 * c + ch], cur.base + ((size_t)c * cur.capacity + i0) * 2 + ch);
+        }
+      if (i0 + lane < n) cp_async16(&stage_mem[wib][stg][192 + lane], quad_ptr(cur, 6, i0 + lane)); // q6 only: q7 (throughput) stays in HBM
+    }
+#else
     const uint32_t i = batch * 32 + lane;
     if (batch < n_batches && i < n) {
 #pragma unroll
       for (int q = 0; q < B200_EXT_QUADS; q++) cp_async16(&stage_mem[wib][stg][q][lane], quad_ptr(cur, q, i));
     }
+#endif
     cp_async_commit();
   };
 
@@ -337,10 +376,17 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
         const uint32_t slot = taken + (uint32_t)__popc(idle & ((1u << lane) - 1u));
         const bool take = !active && slot < count;
         if (take) {
+#if B200_PATH_PAIRED
+          const double2 *sm = &stage_mem[wib][stg][2 * slot];
+          const double2 q0 = sm[0], q1 = sm[1], q2 = sm[64], q3 = sm[65];
+          const float4 q4 = *reinterpret_cast<const float4 *>(sm + 128), q5 = *reinterpret_cast<const float4 *>(sm + 129);
+          const float4 q6 = *reinterpret_cast<const float4 *>(&stage_mem[wib][stg][192 + slot]);
+#else
           const double2 *sm = &stage_mem[wib][stg][0][slot];
           const double2 q0 = sm[0], q1 = sm[32], q2 = sm[64], q3 = sm[96];
           const float4 q4 = *reinterpret_cast<const float4 *>(sm + 128), q5 = *reinterpret_cast<const float4 *>(sm + 160);
           const float4 q6 = *reinterpret_cast<const float4 *>(sm + 192);
+#endif
           idx = base + slot;
           const uint32_t pixel = __float_as_uint(q6.y);
           if (pixel == B200_DEAD) { // a camera sample that produced no ray: nothing to trace, nothing to shade
