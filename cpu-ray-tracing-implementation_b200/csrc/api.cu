@@ -61,11 +61,12 @@ struct b200rt_ctx {
   uint32_t wave_paths = 1u << 24;
   int kill_zero = 1;
   int bvh_leaf = 0;     // 0 = by scene size (profiles/r01_g_tune.txt): 1 primitive per leaf up to 8192 primitives, else 2
-  int refill_lanes = 0; // 0 = by BVH size: fixed 32-ray batches for cache-resident trees, refill at 16 idle lanes from 32 Ki nodes
+  int refill_lanes = 0; // 0 = by BVH size: fixed 32-ray batches for cache-resident trees, refill at 8 idle lanes from 32 Ki nodes
   int extend_blocks = 4;
   int speculative = 0;
   int fuse_miss = 1;
   int bvh_builder = B200RT_BVH_HOST_SAH;
+  int bvh_width = 0; // 0 = by scene size, 2, 4
   int extend_stages = 2; // 1 is within 1 % on RTOW / RTNW / Cornell and 11 % slower on Fox (profiles/r01_h_tune_l1.txt)
   int carveout_pct = -1; // -1 = computed from the kernel's footprint
   // scene
@@ -109,6 +110,10 @@ template <class T> int upload(b200rt_ctx *c, const T *src, size_t count, const T
     int rc_ = upload(c, src, (size_t)(count), dst, what);                                                              \
     if (rc_ != B200RT_OK) return rc_;                                                                                  \
   } while (0)
+
+#ifndef B200_WIDE_FROM_PRIMS
+#define B200_WIDE_FROM_PRIMS 2048 /* scenes above this many primitives are traversed as a BVH4 (their BVH2 does not fit L1) */
+#endif
 
 // Device LBVH (bvh_gpu.cuh): leaves the finished nodes and the entries in leaf order in scene memory.
 int build_bvh_device(b200rt_ctx *c, const FlatScene &fs, DevScene &S, b200rt_bvh_info &info) {
@@ -298,6 +303,10 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
   case B200RT_OPT_EXTEND_BLOCKS: c->extend_blocks = (int)value; return B200RT_OK;
   case B200RT_OPT_SPECULATIVE_LEAF: c->speculative = value != 0; return B200RT_OK;
   case B200RT_OPT_FUSE_MISS: c->fuse_miss = value != 0; return B200RT_OK;
+  case B200RT_OPT_BVH_WIDTH:
+    if (value != 0 && value != 2 && value != 4) return fail(B200RT_ERR_INVALID, "BVH width must be 0 (automatic), 2 or 4");
+    c->bvh_width = (int)value; // takes effect at the next b200rt_upload_scene
+    return B200RT_OK;
   case B200RT_OPT_BVH_BUILDER:
     if (value != B200RT_BVH_HOST_SAH && value != B200RT_BVH_DEVICE_LBVH) return fail(B200RT_ERR_INVALID, "BVH builder must be 0 (host SAH) or 1 (device LBVH)");
     c->bvh_builder = (int)value; // takes effect at the next b200rt_upload_scene
@@ -333,6 +342,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   BuiltBvh bvh;
   std::vector<Entry> ordered;
   bool use_device_builder = false;
+  uint32_t n_nodes4 = 0;
   try {
     Flattener fl(*d);
     fl.run();
@@ -387,6 +397,18 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   } else {
     UP(bvh.nodes.data(), bvh.nodes.size(), &S.bvh, "bvh");
     UP(ordered.data(), ordered.size(), &S.entries, "entries");
+    const int width = c->bvh_width ? c->bvh_width : (ordered.size() > B200_WIDE_FROM_PRIMS ? 4 : 2);
+    if (width == 4 && bvh.root >= 0) {
+      int32_t root4 = B200_EMPTY_ROOT;
+      uint32_t depth4 = 0;
+      const std::vector<BvhNode4> wide = collapse4(bvh, root4, depth4);
+      if (3 * depth4 <= B200_STACK) { // up to three pushes per level; deeper trees keep the BVH2
+        UP(wide.data(), wide.size(), &S.bvh4, "bvh4");
+        bvh.root = root4;
+        n_nodes4 = (uint32_t)wide.size();
+        bvh.max_depth = depth4;
+      }
+    }
   }
   UP(fs.bentries.data(), fs.bentries.size(), &S.bentries, "bentries");
   UP(fs.vol_inst.data(), fs.vol_inst.size(), &S.vol_inst, "vol_inst");
@@ -402,7 +424,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   CU(cudaStreamSynchronize(c->stream)); // host vectors go out of scope
   c->S = S;
   if (!use_device_builder) {
-    c->bvh_info.n_nodes = (uint32_t)bvh.nodes.size();
+    c->bvh_info.n_nodes = n_nodes4 ? n_nodes4 : (uint32_t)bvh.nodes.size(); // the array that is traversed
     c->bvh_info.n_leaves = bvh.n_leaves;
     c->bvh_info.n_prims = (uint32_t)ordered.size();
     c->bvh_info.max_depth = bvh.max_depth;
@@ -628,7 +650,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   wp.max_depth = c->cam.max_depth;
   wp.kill_zero = c->kill_zero;
   wp.fused_miss = (mirror || !c->fuse_miss) ? 0 : c->bg_mode;
-  wp.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 16 : 32);
+  wp.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 8 : 32);
   for (int k = 0; k < 3; k++) wp.bound[k] = c->S.bound[k];
   const DevCamera cam = make_camera(c->cam);
   const int g_gen = grid_for(c, capacity, 256, 8), g_ext = grid_for(c, capacity, 128, 16);
@@ -655,14 +677,16 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
       switch (c->extend_blocks * 2 + (c->speculative ? 1 : 0)) {
       // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
 #define EXT(MAXREG, SPEC, WARPS, STAGES)                                                                               \
-  launch_extend(k_extend_persistent<MAXREG, SPEC, WARPS, STAGES>, c, 65536 / (MAXREG * WARPS * 32), WARPS * 32, WARPS * STAGES * 3584, s, cur, wp)
+  launch_extend(k_extend_persistent<MAXREG, SPEC, WARPS, STAGES, false>, c, 65536 / (MAXREG * WARPS * 32), WARPS * 32, WARPS * STAGES * 3584, s, cur, wp)
       case 12: EXT(80, false, 4, 1); break;  // 24 warps per SM
       case 10: EXT(96, false, 2, 1); break;  // 20 warps
       case 18: EXT(112, false, 2, 1); break; // 18 warps (option value 9: 2-warp CTAs)
       case 34: EXT(120, false, 1, 1); break; // 17 warps (option value 17: 1-warp CTAs)
       case 9: EXT(128, true, 4, 2); break;
       default:
-        if (c->extend_stages == 1 && wp.refill == 32)
+        if (c->S.bvh4)
+          launch_extend(k_extend_persistent<128, false, 4, 2, true>, c, 4, 128, 4 * 2 * 3584, s, cur, wp);
+        else if (c->extend_stages == 1 && wp.refill == 32)
           EXT(128, false, 4, 1);
         else
           EXT(128, false, 4, 2);

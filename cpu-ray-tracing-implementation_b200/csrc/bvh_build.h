@@ -182,4 +182,76 @@ private:
   }
 };
 
+// BVH2 -> BVH4: every kept node adopts its grandchildren, largest box first, until it has four children or only leaves.
+// Child references keep their encoding (inner: index into the NEW array; leaf: unchanged).
+inline std::vector<BvhNode4> collapse4(const BuiltBvh &b2, int32_t &root4, uint32_t &max_depth4) {
+  std::vector<BvhNode4> out;
+  max_depth4 = b2.root == B200_EMPTY_ROOT ? 0 : 1;
+  if (b2.root < 0) { // empty world or a single leaf: nothing to collapse
+    root4 = b2.root;
+    return out;
+  }
+  struct Kid {
+    float box[6];
+    int32_t ref; // BVH2 reference
+  };
+  auto area = [](const float *b) {
+    const double dx = (double)b[1] - b[0], dy = (double)b[3] - b[2], dz = (double)b[5] - b[4];
+    const double a = 2 * (dx * dy + dy * dz + dz * dx);
+    return a == a ? a : 0.0;
+  };
+  struct Job {
+    int32_t node2, slot4;
+    uint32_t depth;
+  };
+  std::vector<Job> todo;
+  out.emplace_back();
+  todo.push_back({b2.root, 0, 1});
+  while (!todo.empty()) {
+    const Job j = todo.back();
+    todo.pop_back();
+    max_depth4 = std::max(max_depth4, j.depth + 1);
+    std::vector<Kid> kids;
+    auto adopt = [&](int32_t n2) {
+      const BvhNode &nd = b2.nodes[n2];
+      Kid l, r;
+      std::memcpy(l.box, nd.lbox, sizeof l.box);
+      std::memcpy(r.box, nd.rbox, sizeof r.box);
+      l.ref = nd.left, r.ref = nd.right;
+      kids.push_back(l);
+      kids.push_back(r);
+    };
+    adopt(j.node2);
+    while (kids.size() < 4) {
+      int best = -1;
+      double best_area = -1;
+      for (size_t k = 0; k < kids.size(); k++)
+        if (kids[k].ref >= 0 && area(kids[k].box) > best_area) best_area = area(kids[k].box), best = (int)k;
+      if (best < 0) break;
+      const int32_t n2 = kids[best].ref;
+      kids.erase(kids.begin() + best);
+      adopt(n2);
+    }
+    BvhNode4 nd;
+    std::memset(&nd, 0, sizeof nd);
+    for (int k = 0; k < 4; k++) {
+      if (k < (int)kids.size()) {
+        nd.x0[k] = kids[k].box[0], nd.x1[k] = kids[k].box[1], nd.y0[k] = kids[k].box[2], nd.y1[k] = kids[k].box[3], nd.z0[k] = kids[k].box[4], nd.z1[k] = kids[k].box[5];
+        if (kids[k].ref >= 0) {
+          nd.child[k] = (int32_t)out.size();
+          out.emplace_back();
+          todo.push_back({kids[k].ref, nd.child[k], j.depth + 1});
+        } else {
+          nd.child[k] = kids[k].ref;
+        }
+      } else {
+        nd.child[k] = B200_EMPTY_ROOT;
+      }
+    }
+    out[j.slot4] = nd;
+  }
+  root4 = 0;
+  return out;
+}
+
 } // namespace b200

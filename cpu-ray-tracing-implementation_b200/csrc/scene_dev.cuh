@@ -54,6 +54,17 @@ struct __align__(16) BvhNode {
   int32_t pad[2];
 };
 static_assert(sizeof(BvhNode) == 64, "BvhNode must be half a 128-byte line");
+
+// BVH4 node, 128 bytes = one cache line = eight 128-bit loads: up to four children, planes stored per coordinate so that
+// child k's box is lane k of six float4s.  Made by collapsing the BVH2 (bvh_build.h: collapse4); same child references,
+// an absent child is B200_EMPTY_ROOT.  Halves the number of DEPENDENT node fetches per ray, which is what a ray pays for
+// in trees that do not fit L1 (Sponza-sized scenes: long-scoreboard stalls dominate the BVH2 walk).
+struct __align__(16) BvhNode4 {
+  float x0[4], x1[4], y0[4], y1[4], z0[4], z1[4];
+  int32_t child[4];
+  int32_t pad[4];
+};
+static_assert(sizeof(BvhNode4) == 128, "BvhNode4 must be one 128-byte line");
 static_assert(sizeof(Entry) == 16 && sizeof(VolInst) == 16 && sizeof(ChainOp) == 32, "layout");
 
 #define B200_EMPTY_ROOT (-2147483647 - 1)
@@ -81,6 +92,7 @@ struct DevScene {
   int32_t light_kind, light_index, background_tex;
   // (2) compacted
   const BvhNode *bvh;
+  const BvhNode4 *bvh4; // non-null: traverse this (bvh_root indexes it) instead of bvh
   int32_t bvh_root; // child-reference encoding; B200_EMPTY_ROOT for an empty world
   uint32_t n_bvh_nodes;
   const Entry *entries;  // BVH leaf order

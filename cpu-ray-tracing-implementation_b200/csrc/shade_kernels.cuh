@@ -31,8 +31,16 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
   const uint32_t n = c->q_count[KIND];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int par = 0;
+  // the queue index of the NEXT slice is fetched one iteration ahead (one register), which takes the first of the dependent
+  // loads (queue -> path -> hit -> entry -> ...) off every iteration's critical path
+  uint32_t i_next = blockIdx.x * 128 + threadIdx.x < n ? queue[blockIdx.x * 128 + threadIdx.x] : 0u;
   for (uint32_t bbase = blockIdx.x * 128; bbase < n; bbase += gridDim.x * 128, par ^= 1) {
     const uint32_t j = bbase + threadIdx.x;
+    const uint32_t i_cur = i_next;
+    {
+      const uint32_t jn = j + gridDim.x * 128;
+      if (jn < n) i_next = queue[jn];
+    }
 #if B200_SHADE_PREFETCH
     {
       const uint32_t jn = j + gridDim.x * 128;
@@ -49,7 +57,7 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
     V T;
     uint32_t pixel = 0, sample = 0, bounce = 0;
     if (j < n) {
-      const uint32_t i = queue[j];
+      const uint32_t i = i_cur;
       const PathHead ph = load_head(cur, i, &T);
       const Ray r = ph.r;
       pixel = ph.pixel;

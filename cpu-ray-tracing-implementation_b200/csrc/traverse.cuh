@@ -134,6 +134,40 @@ DEV int32_t node_step(const DevScene &S, int32_t cur, const RaySetup &rs, float 
   return hl ? ch.x : (hr ? ch.y : B200_DONE);
 }
 
+// One BVH4 node: test up to four children, return the nearest accepted one (or B200_DONE) and push the others, farthest
+// first, so that they pop nearest first.
+DEV void cswap4(float &ka, int32_t &ca, float &kb, int32_t &cb) {
+  const bool s = kb < ka;
+  const float k0 = s ? kb : ka, k1 = s ? ka : kb;
+  const int32_t c0 = s ? cb : ca, c1 = s ? ca : cb;
+  ka = k0, kb = k1, ca = c0, cb = c1;
+}
+DEV int32_t node_step4(const DevScene &S, int32_t cur, const RaySetup &rs, float lo32, float hi32, int32_t *stack, int &sp) {
+  const float4 *q = reinterpret_cast<const float4 *>(S.bvh4 + cur);
+  const float4 X0 = __ldg(q), X1 = __ldg(q + 1), Y0 = __ldg(q + 2), Y1 = __ldg(q + 3), Z0 = __ldg(q + 4), Z1 = __ldg(q + 5);
+  const int4 ch = __ldg(reinterpret_cast<const int4 *>(q + 6));
+  const float INF32 = __int_as_float(0x7f800000);
+  float n0, f0, n1, f1, n2, f2, n3, f3;
+  slab32(X0.x, X1.x, Y0.x, Y1.x, Z0.x, Z1.x, rs, lo32, hi32, n0, f0);
+  slab32(X0.y, X1.y, Y0.y, Y1.y, Z0.y, Z1.y, rs, lo32, hi32, n1, f1);
+  slab32(X0.z, X1.z, Y0.z, Y1.z, Z0.z, Z1.z, rs, lo32, hi32, n2, f2);
+  slab32(X0.w, X1.w, Y0.w, Y1.w, Z0.w, Z1.w, rs, lo32, hi32, n3, f3);
+  // key = entry parameter of an accepted child (kept below +inf), +inf for a rejected or absent one
+  const float BIG = 3.0e38f;
+  float k0 = (n0 <= f0 && ch.x != B200_DONE) ? fminf(n0, BIG) : INF32, k1 = (n1 <= f1 && ch.y != B200_DONE) ? fminf(n1, BIG) : INF32;
+  float k2 = (n2 <= f2 && ch.z != B200_DONE) ? fminf(n2, BIG) : INF32, k3 = (n3 <= f3 && ch.w != B200_DONE) ? fminf(n3, BIG) : INF32;
+  int32_t c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
+  cswap4(k0, c0, k1, c1);
+  cswap4(k2, c2, k3, c3);
+  cswap4(k0, c0, k2, c2);
+  cswap4(k1, c1, k3, c3);
+  cswap4(k1, c1, k2, c2);
+  if (k3 < INF32 && sp < B200_STACK) stack[sp++] = c3;
+  if (k2 < INF32 && sp < B200_STACK) stack[sp++] = c2;
+  if (k1 < INF32 && sp < B200_STACK) stack[sp++] = c1;
+  return k0 < INF32 ? c0 : B200_DONE;
+}
+
 // world.hit(r, interval(lo, hi), rec) -> (entry, t); entry < 0 on a miss.
 DEV Best trace_closest(const DevScene &S, const Ray &r, double lo, double hi, const Stream &st, int bounce) {
   Best best;
@@ -149,7 +183,7 @@ DEV Best trace_closest(const DevScene &S, const Ray &r, double lo, double hi, co
   int32_t cur = S.bvh_root;
   for (;;) {
     while (cur >= 0) { // inner nodes
-      cur = node_step(S, cur, rs, lo32, hi32, stack, sp);
+      cur = S.bvh4 ? node_step4(S, cur, rs, lo32, hi32, stack, sp) : node_step(S, cur, rs, lo32, hi32, stack, sp);
       if (cur == B200_DONE && sp > 0) cur = stack[--sp];
     }
     if (cur == B200_DONE) return best;

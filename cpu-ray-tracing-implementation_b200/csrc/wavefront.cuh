@@ -299,7 +299,8 @@ DEV void cp_async_wait_all() {
 // STAGES: 2 = the next batch is always in flight (needed when lanes refill mid-batch); 1 = the single stage is refilled as
 // soon as its 32 rays have been taken into registers.  Shared memory is carved out of the L1 that caches the BVH, so the
 // smaller footprint (14 KB instead of 28 KB per CTA) is not free to give away: see DESIGN.md.
-template <int MAXREG, bool SPEC, int WARPS, int STAGES>
+// WIDE: the tree is the BVH4 of scene_dev.cuh (S.bvh4) instead of the BVH2.
+template <int MAXREG, bool SPEC, int WARPS, int STAGES, bool WIDE>
 __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp) {
 #if B200_PATH_PAIRED
   __shared__ __align__(32) double2 stage_mem[WARPS][STAGES][224]; // warp x stage x {3 columns x 32 paths x 2 quads, then q6 of 32 paths}: 3.5 KB
@@ -430,7 +431,7 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
             node = sp > 0 ? stack[--sp] : B200_DONE;
             continue;
           }
-          node = node_step(S, node, rs, lo32, hi32, stack, sp);
+          node = WIDE ? node_step4(S, node, rs, lo32, hi32, stack, sp) : node_step(S, node, rs, lo32, hi32, stack, sp);
           if (node == B200_DONE && sp > 0) node = stack[--sp];
         }
         while (pending != B200_DONE) { // the postponed leaf, then whatever leaves follow directly
@@ -445,7 +446,7 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
         }
       } else {
         while (node >= 0) {
-          node = node_step(S, node, rs, lo32, hi32, stack, sp);
+          node = WIDE ? node_step4(S, node, rs, lo32, hi32, stack, sp) : node_step(S, node, rs, lo32, hi32, stack, sp);
           if (node == B200_DONE && sp > 0) node = stack[--sp];
         }
         if (node != B200_DONE) {

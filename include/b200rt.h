@@ -226,7 +226,8 @@ typedef enum b200rt_option {
   B200RT_OPT_EXTEND_STAGES = 9, /* tuning: ray batches staged in shared memory per warp, 2 (default) or 1; lane refill always uses 2 */
   B200RT_OPT_SMEM_CARVEOUT = 10, /* tuning: shared-memory carve-out of the extend kernel in percent, -1 (default) = smallest that fits */
   B200RT_OPT_BVH_BUILDER = 11,  /* who builds the compacted BVH that replaces bvh_node's constructor (src/bvh_node.h:18-47): B200RT_BVH_HOST_SAH (default) or B200RT_BVH_DEVICE_LBVH */
-  B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 16 from 32 Ki BVH nodes) */
+  B200RT_OPT_BVH_WIDTH = 12,    /* children per node of the traversed tree: 2, 4 (collapsed from the host SAH BVH2), 0 (default) = 4 above 2048 primitives */
+  B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 8 from 32 Ki BVH nodes) */
 } b200rt_option;
 
 #define B200RT_BVH_HOST_SAH 0    /* binned SAH over three axes on the host: best tree, ~0.5 us per primitive */

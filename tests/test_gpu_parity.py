@@ -407,3 +407,30 @@ def test_reference_side_binding_end_to_end(name, tmp_path):
     assert got_ints.shape == want_ints.shape == (H * W * 3,)
     assert (np.abs(got_ints - want_ints) <= 1).all() and (got_ints != want_ints).mean() < 1e-3  # fp64 atomic order can move a value across an integer boundary
     rs.close()
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_bvh4_gives_the_same_hits(name):
+    """B200RT_OPT_BVH_WIDTH = 4 (the BVH2 collapsed into 128-byte four-child nodes): a different walk, the same records."""
+    g = golden(name)
+    c = pkg.backend.Context(0)
+    try:
+        c.set_option(abi.OPT_BVH_WIDTH, 4)
+        c.upload_scene(g.scene)
+        out = c.trace(g["trace_rays"], seed=99)
+        ref = {k: g["trace_" + k] for k in ("prim", "t", "uv", "front", "p", "normal")}
+        keep = np.ones(len(out["prim"]), bool)
+        if name in VOLUME_SCENES:
+            vol = np.array(sorted(g.volume_prims()))
+            keep = ~np.isin(out["prim"], vol) & ~np.isin(ref["prim"], vol)
+        check_records(name, out, ref, keep)
+        c.set_camera(g.cam_small)
+        img, st = c.render(5, 0, 4)
+        c.set_option(abi.OPT_BVH_WIDTH, 2)
+        c.upload_scene(g.scene)
+        img0, st0 = c.render(5, 0, 4)
+        assert st["rays"] == st0["rays"]
+        fin = np.isfinite(img0)
+        assert np.array_equal(fin, np.isfinite(img)) and np.allclose(img[fin], img0[fin], rtol=1e-12, atol=1e-12)
+    finally:
+        c.close()

@@ -72,10 +72,12 @@ def main():
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--cpu", action="store_true", help="add the CPU baseline of every scene (see cpu_baseline)")
     ap.add_argument("--builder", type=int, default=0, help="0 = host SAH BVH (default), 1 = device LBVH (csrc/bvh_gpu.cuh)")
+    ap.add_argument("--width", type=int, default=0, help="BVH width: 0 = automatic, 2, 4")
     ap.add_argument("--mirror", action="store_true", help="also time the node-for-node mirror traversal (parity arbiter)")
     args = ap.parse_args()
     ctx = pkg.backend.Context(0)
     ctx.set_option(abi.OPT_BVH_BUILDER, args.builder)
+    ctx.set_option(abi.OPT_BVH_WIDTH, args.width)
     for name in args.scenes.split(","):
         t0 = time.perf_counter()
         sc, cam = load(name)

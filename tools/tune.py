@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--leaf", default="0")
     ap.add_argument("--stages", default="1", help="ray batches staged per warp: 1, 2 or 1,2")
     ap.add_argument("--carveout", default="-1", help="shared-memory carve-out percent of the extend kernel (-1 = automatic)")
+    ap.add_argument("--width", type=int, default=0, help="BVH width: 0 = automatic, 2, 4")
     ap.add_argument("--spec", default="0", help="speculative (postponed-leaf) traversal: 0, 1 or 0,1")
     a = ap.parse_args()
     scene, cam = load(a.scene)
@@ -48,6 +49,7 @@ def main():
     for leaf in ints(a.leaf):
         ctx = pkg.backend.Context(0)
         ctx.set_option(abi.OPT_BVH_LEAF_SIZE, leaf)
+        ctx.set_option(abi.OPT_BVH_WIDTH, a.width)
         ctx.upload_scene(scene)
         ctx.set_camera(cam)
         for wave, refill, blocks, spec, stages, carve in itertools.product(ints(a.wave), ints(a.refill), ints(a.blocks), ints(a.spec), ints(a.stages),
@@ -64,7 +66,7 @@ def main():
                 st = ctx.render_device(0x5EED, 0, a.spp, accum.data_ptr(), stream, want_stats=True)
                 if best is None or st["gpu_ms"] < best["gpu_ms"]:
                     best = st
-            print(json.dumps({"scene": a.scene, "spp": a.spp, "leaf": leaf, "wave_log2": wave, "refill": refill, "blocks": blocks, "spec": spec, "stages": stages, "carveout": carve,
+            print(json.dumps({"scene": a.scene, "spp": a.spp, "leaf": leaf, "wave_log2": wave, "refill": refill, "blocks": blocks, "spec": spec, "width": a.width, "stages": stages, "carveout": carve,
                               "mrays_per_s": best["rays"] / best["gpu_ms"] / 1e3, "gpu_ms": best["gpu_ms"], "extend_ms": best["extend_ms"],
                               "waves": best["waves"]}), flush=True)
         ctx.close()
