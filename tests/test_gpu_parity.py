@@ -434,3 +434,52 @@ def test_bvh4_gives_the_same_hits(name):
         assert np.array_equal(fin, np.isfinite(img)) and np.allclose(img[fin], img0[fin], rtol=1e-12, atol=1e-12)
     finally:
         c.close()
+
+
+def _empty_world(g):
+    """A hittable_list with no objects (src/hittable_list.h:20-31 returns false for every ray) under the scene's background."""
+    import copy
+
+    s = copy.copy(g.scene)
+    s.nodes = g.scene.nodes[:1].copy()
+    s.nodes["kind"][0], s.nodes["a"][0], s.nodes["b"][0] = abi.NODE_LIST, 0, 0
+    s.list_children = g.scene.list_children[:0].copy()
+    s.root = 0
+    s.n_primitives = 0
+    return s
+
+
+@pytest.mark.parametrize("builder", [abi.BVH_HOST_SAH, abi.BVH_DEVICE_LBVH])
+@pytest.mark.parametrize("width", [2, 4])
+def test_edge_cases_empty_and_single_primitive_worlds(builder, width, build_oracle):
+    """Empty world: every ray misses, every sample is the background (here solid white: sum == spp).  One-primitive world:
+    the root of the compacted tree is a leaf.  Empty ray batches and empty sample ranges are no-ops.  All against the oracle."""
+    g = golden("white_sphere")
+    with pkg.backend.Context(0) as c:
+        c.set_option(abi.OPT_BVH_BUILDER, builder)
+        c.set_option(abi.OPT_BVH_WIDTH, width)
+        # one primitive
+        c.upload_scene(g.scene)
+        info = c.bvh_info()
+        assert info["n_prims"] == 1 and info["n_leaves"] == 1
+        out, ref = c.trace(g["trace_rays"], seed=99), build_oracle.trace(g.scene, g["trace_rays"], seed=99)
+        for k in ("prim", "t", "p", "normal", "front"):
+            assert same(out[k], ref[k]).all(), k
+        assert (out["prim"] >= 0).any() and (out["prim"] < 0).any()
+        c.set_camera(g.cam_small)
+        img, st = c.render(3, 0, 4)
+        want = build_oracle.render(g.scene, g.cam_small, 3, 0, 4)
+        assert np.allclose(img, want["sum"], rtol=1e-9, atol=1e-12) and st["rays"] == want["stats"]["rays"]
+        # nothing to do
+        assert len(c.trace(np.zeros((0, 7)))["prim"]) == 0
+        z, stz = c.render(3, 5, 5)
+        assert not z.any() and stz["samples"] == 0 and stz["rays"] == 0
+        # empty world
+        e = _empty_world(g)
+        c.upload_scene(e)
+        assert c.bvh_info()["n_prims"] == 0
+        out = c.trace(g["trace_rays"], seed=99)
+        assert (out["prim"] == -1).all()
+        img, st = c.render(3, 0, 4)
+        want = build_oracle.render(e, g.cam_small, 3, 0, 4)
+        assert np.allclose(img, want["sum"], rtol=1e-12, atol=0) and st["rays"] == st["samples"] == want["stats"]["rays"]
