@@ -27,7 +27,7 @@ sys.path.insert(0, ROOT)
 SCENE = "rtow"
 WORKLOAD = "RTOW final scene: 487 spheres (lambertian/metal/dielectric), lens DOF camera, 1200x675, 500 spp, max depth 50"
 METRIC, UNIT = "Mrays/s on RTOW final scene (1200x675, 500 spp, depth 50); Msamples/s alongside", "Mrays/s"
-TRAFFIC_BYTES_PER_RAY = 2143.75e6 / 16777216  # profiles/r01_i_extend_ncu_full.txt: dram__bytes_read.sum 1880.8 MB + dram__bytes_write.sum 263.0 MB of one full 16 Mi-ray launch = 127.8 B/ray
+TRAFFIC_BYTES_PER_RAY = 2415.63e6 / 16777216  # profiles/r01_p_extend_ncu_full.txt: dram__bytes_read.sum 2150.4 MB + dram__bytes_write.sum 265.2 MB of one full 16 Mi-ray launch = 144 B/ray (q7 shares q6's 32-byte sector)
 EXTEND_BYTES_PER_RAY = 128  # k_extend_persistent: reads 7 of the 8 path quads (ray, time, box-filter constants, ids: 112 B), writes one HitRef (16 B)
 
 
@@ -235,7 +235,7 @@ def run_ours(args):
                              "extend_share_of_step": st["extend_ms"] / st["gpu_ms"],
                              "algorithmic_bytes_per_launch": st["rays"] * EXTEND_BYTES_PER_RAY / max(1, st["waves"]), "launches": st["waves"],
                              "note": "issue/latency bound, not HBM bound (fp32 box filter + binary64 reference-order leaf tests over an L1/L2-resident BVH); "
-                                     "traffic = dram read+write per ray of a full launch from profiles/r01_i_extend_ncu_full.txt (ncu --set full) x mean rays per launch; see DESIGN.md"},
+                                     "traffic = dram read+write per ray of a full launch from profiles/r01_p_extend_ncu_full.txt (ncu --set full) x mean rays per launch; see DESIGN.md"},
                 "e2e": e2e, "gpu_launches": int(launches * args.steps), "clocks": clocks}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
