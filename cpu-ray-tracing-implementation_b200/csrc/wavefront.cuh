@@ -1,9 +1,10 @@
 // wavefront.cuh — the sample loop of camera::render (src/camera.h:158-172) as a wavefront of paths.
 //
-// A pool of `capacity` path slots lives in HBM as structure-of-arrays (coalesced 8-byte columns).  One wave is
+// A pool of `capacity` path slots lives in HBM as structure-of-arrays (four columns of 32 bytes per path).  One wave is
 //   k_generate  : refill free slots with fresh camera rays (generate_ray per camera mode, camera.cuh)
-//   k_extend    : closest hit of every live ray (traverse.cuh), then sort the ray's index into the queue of
-//                 the material kind it hit (or the miss queue) with warp ballot/popc aggregated appends
+//   k_extend    : closest hit of every live ray (traverse.cuh): persistent warps, rays staged through shared memory
+//   k_classify  : sort every path's index into the queue of the material kind it hit (or the miss queue):
+//                 ballot/popc ranking per warp, one global atomic per queue per 2048-path chunk
 //   k_shade<K>  : one launch per material kind over its queue: rebuild the hit record, scatter / emit
 //                 (shading.cuh), accumulate finished paths into the per-pixel fp64 sums and append the
 //                 survivors, compacted, to the other pool
@@ -28,11 +29,8 @@ struct WaveCtl {
   uint32_t q_count[8];
 };
 
-// Path state = eight 16-byte columns ("quads") of `capacity` elements each: every access is one 128-bit load or
-// store, a warp working on consecutive paths (extend batches, compacted appends of the shade kernels) moves 512
-// contiguous bytes per instruction, and the queue-ordered gathers of the shade kernels touch 6 sectors per path
-// instead of 13.  The fp32 box-filter constants (traverse.cuh) are computed by the PRODUCER of the ray (k_generate /
-// k_shade) and ride along in quads 4-6, so the extend kernel starts traversing straight away.
+// Path state = eight 16-byte "quads" per path.  The fp32 box-filter constants (traverse.cuh) are computed by the PRODUCER
+// of the ray (k_generate / k_shade) and ride along in quads 4-6, so the extend kernel starts traversing straight away.
 //   q0 {o.x o.y}  q1 {o.z d.x}  q2 {d.y d.z}  q3 {time T.x}  q4 {ix iy iz c0x}  q5 {c1x c0y c1y c0z}
 //   q6 {c1z pixel sample bounce}  q7 {T.y T.z}
 #define B200_PATH_QUADS 8

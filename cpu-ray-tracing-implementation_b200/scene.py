@@ -289,70 +289,68 @@ def reference_like_bvh(boxes):
     return inner, root
 
 
-def sponza_standin_scene(n_triangles=SPONZA_TRIANGLES, seed=7):
-    """BASELINE.json configs[4] as the reference's sponza() builds it (src/main.cc:439-489) over the stand-in mesh:
-    every triangle lambertian white, quad light (0,1200,0) 500x500 emitting 10, one bvh_node over everything, the quad
-    passed as `light`.  Labelled "Sponza-standin": the real Sponza.bin is missing from the reference checkout."""
-    t32 = sponza_standin_triangles(n_triangles, seed)
-    t = t32.astype(np.float64)
+def triangle_scene(t32, materials, textures, tri_mat=None, light=None, background_tex=-1, name="mesh"):
+    """A scene as the reference's mesh functions build it (glass_fox src/main.cc:345-400, sponza src/main.cc:439-498): one
+    `triangle` per row of `t32` (float32 (n, 9), e.g. from gltf.load_triangles), optionally one quad `light` = (corner, u, v,
+    material index) that is both in the world and passed as `light`, ONE bvh_node over everything with the reference's
+    x-sorted median splits (src/bvh_node.h:18-47).  `materials` / `textures` are tables in abi.material_dtype / abi.texture_dtype."""
+    t = np.asarray(t32, dtype=np.float32).reshape(-1, 9).astype(np.float64)
     p0, p1, p2 = t[:, 0:3], t[:, 3:6], t[:, 6:9]
     e1, e2 = p1 - p0, p2 - p0
     c = np.stack([e1[:, 1] * e2[:, 2] - e1[:, 2] * e2[:, 1], e1[:, 2] * e2[:, 0] - e1[:, 0] * e2[:, 2], e1[:, 0] * e2[:, 1] - e1[:, 1] * e2[:, 0]], axis=1)
     with np.errstate(invalid="ignore", divide="ignore"):
         nrm = c / np.sqrt(c[:, 0] * c[:, 0] + c[:, 1] * c[:, 1] + c[:, 2] * c[:, 2])[:, None]  # unit_vector(cross(p1-p0, p2-p0)), src/triangle.h:24
     s = Scene()
-    s.name = "sponza-standin"
+    s.name = name
     s.tris = np.ascontiguousarray(np.concatenate([t, nrm], axis=1))
-    s.tri_mat = np.zeros(len(t), dtype="<i4")
-    # quad light: corner, u, v, unorm, w = n / dot(n, n), D = dot(unorm, corner), area (include/b200rt.h B200RT_QUAD_STRIDE)
-    corner, u, v = np.array([0.0, 1200.0, 0.0]), np.array([500.0, 0.0, 0.0]), np.array([0.0, 0.0, 500.0])
-    nq = np.array([u[1] * v[2] - u[2] * v[1], u[2] * v[0] - u[0] * v[2], u[0] * v[1] - u[1] * v[0]])
-    area = float(np.sqrt(nq[0] * nq[0] + nq[1] * nq[1] + nq[2] * nq[2]))
-    unorm = nq / area
-    w = nq / (nq[0] * nq[0] + nq[1] * nq[1] + nq[2] * nq[2])
-    q = np.zeros((1, abi.QUAD_STRIDE))
-    q[0, 0:3], q[0, 3:6], q[0, 6:9], q[0, 9:12], q[0, 12:15] = corner, u, v, unorm, w
-    q[0, 15] = unorm[0] * corner[0] + unorm[1] * corner[1] + unorm[2] * corner[2]
-    q[0, 16] = area
-    s.quads = q
-    s.quad_mat = np.array([1], dtype="<i4")
-    s.textures = np.zeros(2, dtype=abi.texture_dtype)
-    s.textures["kind"] = abi.TEX_SOLID
-    s.textures["c0"][0] = 1.0
-    s.textures["c0"][1] = 10.0
-    s.materials = np.zeros(2, dtype=abi.material_dtype)
-    s.materials["kind"] = [abi.MAT_LAMBERTIAN, abi.MAT_DIFFUSE_LIGHT]
-    s.materials["tex"] = [0, 1]
-    # object boxes: triangle = aabb(min, max) unpadded (src/triangle.h:42-48); quad = enclose of its two diagonals (src/quad.h:19-21)
+    s.tri_mat = np.zeros(len(t), dtype="<i4") if tri_mat is None else np.ascontiguousarray(tri_mat, dtype="<i4")
+    s.textures = np.ascontiguousarray(textures, dtype=abi.texture_dtype)
+    s.materials = np.ascontiguousarray(materials, dtype=abi.material_dtype)
     nt = len(t)
-    boxes = np.empty((nt + 1, 6))
+    n_obj = nt + (1 if light is not None else 0)
+    # object boxes: triangle = aabb(min, max) unpadded (src/triangle.h:42-48); quad = enclose of its two diagonals (src/quad.h:19-21)
+    boxes = np.empty((n_obj, 6))
     P = t.reshape(nt, 3, 3)
     boxes[:nt, 0::2] = P.min(axis=1)
     boxes[:nt, 1::2] = P.max(axis=1)
-    qb = np.stack([corner, corner + u, corner + v, corner + u + v])
-    qbox = np.empty(6)
-    qbox[0::2], qbox[1::2] = qb.min(axis=0), qb.max(axis=0)
-    for k in range(3):
-        if qbox[2 * k + 1] - qbox[2 * k] < 0.0001:
-            qbox[2 * k] -= 0.00005
-            qbox[2 * k + 1] += 0.00005
-    boxes[nt] = qbox
+    if light is not None:
+        # quad row: corner, u, v, unorm, w = n / dot(n, n), D = dot(unorm, corner), area (include/b200rt.h B200RT_QUAD_STRIDE)
+        corner, u, v = (np.asarray(x, dtype=np.float64) for x in light[:3])
+        nq = np.array([u[1] * v[2] - u[2] * v[1], u[2] * v[0] - u[0] * v[2], u[0] * v[1] - u[1] * v[0]])
+        area = float(np.sqrt(nq[0] * nq[0] + nq[1] * nq[1] + nq[2] * nq[2]))
+        unorm = nq / area
+        w = nq / (nq[0] * nq[0] + nq[1] * nq[1] + nq[2] * nq[2])
+        q = np.zeros((1, abi.QUAD_STRIDE))
+        q[0, 0:3], q[0, 3:6], q[0, 6:9], q[0, 9:12], q[0, 12:15] = corner, u, v, unorm, w
+        q[0, 15] = unorm[0] * corner[0] + unorm[1] * corner[1] + unorm[2] * corner[2]
+        q[0, 16] = area
+        s.quads = q
+        s.quad_mat = np.array([int(light[3])], dtype="<i4")
+        qb = np.stack([corner, corner + u, corner + v, corner + u + v])
+        qbox = np.empty(6)
+        qbox[0::2], qbox[1::2] = qb.min(axis=0), qb.max(axis=0)
+        for k in range(3):
+            if qbox[2 * k + 1] - qbox[2 * k] < 0.0001:
+                qbox[2 * k] -= 0.00005
+                qbox[2 * k + 1] += 0.00005
+        boxes[nt] = qbox
     inner, root = reference_like_bvh(boxes)
     m = len(inner)
-    nodes = np.zeros(m + nt + 1, dtype=abi.node_dtype)
-    # leaves first: node i (< nt) = triangle i, node nt = the quad; inner node k lives at nt + 1 + k
+    nodes = np.zeros(m + n_obj, dtype=abi.node_dtype)
+    # leaves first: node i (< nt) = triangle i, node nt = the quad; inner node k lives at n_obj + k
     nodes["kind"][:nt] = abi.NODE_TRIANGLE
     nodes["a"][:nt] = np.arange(nt)
-    nodes["kind"][nt] = abi.NODE_QUAD
-    nodes["a"][nt] = 0
+    if light is not None:
+        nodes["kind"][nt] = abi.NODE_QUAD
+        nodes["a"][nt] = 0
     ia = np.array([x[0] for x in inner], dtype=np.int64)
     ib = np.array([x[1] for x in inner], dtype=np.int64)
-    nodes["kind"][nt + 1:] = abi.NODE_BVH
-    nodes["a"][nt + 1:] = np.where(ia >= 0, ia + nt + 1, ~ia)
-    nodes["b"][nt + 1:] = np.where(ib >= 0, ib + nt + 1, ~ib)
-    nodes["f"][nt + 1:] = np.array([x[2] for x in inner])
+    nodes["kind"][n_obj:] = abi.NODE_BVH
+    nodes["a"][n_obj:] = np.where(ia >= 0, ia + n_obj, ~ia)
+    nodes["b"][n_obj:] = np.where(ib >= 0, ib + n_obj, ~ib)
+    nodes["f"][n_obj:] = np.array([x[2] for x in inner])
     # primitive ids = order of first visit in the reference's left-to-right depth-first walk
-    ids = np.full(nt + 1, -1, dtype=np.int64)
+    ids = np.full(n_obj, -1, dtype=np.int64)
     nxt = 0
     stack = [root]
     while stack:
@@ -365,11 +363,26 @@ def sponza_standin_scene(n_triangles=SPONZA_TRIANGLES, seed=7):
             continue
         stack.append(int(ib[k]))
         stack.append(int(ia[k]))
-    nodes["c"][: nt + 1] = ids
+    nodes["c"][:n_obj] = ids
     s.nodes = nodes
-    s.root = nt + 1 + root
-    s.n_primitives = nt + 1
-    s.light_kind = abi.LIGHT_QUAD
+    s.root = n_obj + root
+    s.n_primitives = n_obj
+    s.light_kind = abi.LIGHT_QUAD if light is not None else abi.LIGHT_NONE
     s.light_index = 0
-    s.background_tex = -1
+    s.background_tex = background_tex
     return s
+
+
+def sponza_standin_scene(n_triangles=SPONZA_TRIANGLES, seed=7):
+    """BASELINE.json configs[4] as the reference's sponza() builds it (src/main.cc:439-489) over the stand-in mesh:
+    every triangle lambertian white, quad light (0,1200,0) 500x500 emitting 10, one bvh_node over everything, the quad
+    passed as `light`.  Labelled "Sponza-standin": the real Sponza.bin is missing from the reference checkout."""
+    textures = np.zeros(2, dtype=abi.texture_dtype)
+    textures["kind"] = abi.TEX_SOLID
+    textures["c0"][0] = 1.0
+    textures["c0"][1] = 10.0
+    materials = np.zeros(2, dtype=abi.material_dtype)
+    materials["kind"] = [abi.MAT_LAMBERTIAN, abi.MAT_DIFFUSE_LIGHT]
+    materials["tex"] = [0, 1]
+    return triangle_scene(sponza_standin_triangles(n_triangles, seed), materials, textures, light=((0.0, 1200.0, 0.0), (500.0, 0.0, 0.0), (0.0, 0.0, 500.0), 1),
+                          name="sponza-standin")

@@ -5,7 +5,7 @@
 //
 // Parity status: PINNED.  The reference ships no golden vectors, so this file is
 // pinned against the reference itself compiled here (oracle/_ref, built from /root/reference/src):
-// tests/test_oracle_vs_reference.py requires bit-identical hit records (id, t, u, v, p, normal,
+// tests/test_oracle_golden.py requires bit-identical hit records (id, t, u, v, p, normal,
 // front_face), camera rays and texture lookups, and statistically identical images; the committed
 // fixtures under tests/golden/ carry the reference's outputs to machines without /root/reference.
 //
