@@ -70,6 +70,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="spp slice per scene (default: sized to ~0.5 G samples, at most the config's)")
     ap.add_argument("--scenes", default="cornell,rtow,rtnw,fox,sponza")
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--full", action="store_true", help="time every config at its full spp (C5 alone is 34 G samples: about a minute on one B200)")
     ap.add_argument("--cpu", action="store_true", help="add the CPU baseline of every scene (see cpu_baseline)")
     ap.add_argument("--builder", type=int, default=0, help="0 = host SAH BVH (default), 1 = device LBVH (csrc/bvh_gpu.cuh)")
     ap.add_argument("--width", type=int, default=0, help="BVH width: 0 = automatic, 2, 4")
@@ -83,7 +84,7 @@ def main():
         sc, cam = load(name)
         t_load = time.perf_counter() - t0
         npix = cam.image_width * cam.image_height
-        spp = args.spp or max(1, min(cam.samples_per_pixel, int(5e8 // npix)))
+        spp = cam.samples_per_pixel if args.full else (args.spp or max(1, min(cam.samples_per_pixel, int(5e8 // npix))))
         t0 = time.perf_counter()
         ctx.upload_scene(sc)
         t_up = time.perf_counter() - t0
