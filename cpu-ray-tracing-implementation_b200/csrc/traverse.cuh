@@ -117,6 +117,20 @@ DEV void leaf_test(const DevScene &S, int32_t ref, const Ray &r, double lo, doub
   }
 }
 
+// Experiment (-DB200_PUSH_PREFETCH=1): a reference that goes onto the stack will be read some node steps later, so ask for
+// its line now (prefetch.global.L1: no register, no wait).  Measured on B200 (profiles/r01_o_bvh4.jsonl): SLOWER on every
+// scene (Sponza stand-in 1525 vs 1597, RTNW 2004 vs 2079, RTOW 5542 vs 5617 Mrays/s): about half of the pushed references
+// are culled before they are popped, and their lines evict nodes that are in use.  Off.
+#ifndef B200_PUSH_PREFETCH
+#define B200_PUSH_PREFETCH 0
+#endif
+DEV void prefetch_ref(const DevScene &S, int32_t ref, bool wide) {
+#if B200_PUSH_PREFETCH && !defined(B200_HOST_EMU)
+  const void *p = ref >= 0 ? (wide ? (const void *)(S.bvh4 + ref) : (const void *)(S.bvh + ref)) : (const void *)(S.entries + ((uint32_t)~ref >> 3));
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
+}
+
 // One inner node: test both children, return the nearer accepted child (or B200_DONE) and push the other.
 DEV int32_t node_step(const DevScene &S, int32_t cur, const RaySetup &rs, float lo32, float hi32, int32_t *stack, int &sp) {
   const float4 *q = reinterpret_cast<const float4 *>(S.bvh + cur);
@@ -128,7 +142,9 @@ DEV int32_t node_step(const DevScene &S, int32_t cur, const RaySetup &rs, float 
   const bool hl = ln <= lf, hr = rn <= rf;
   if (hl && hr) {
     const bool left_first = ln <= rn;
-    if (sp < B200_STACK) stack[sp++] = left_first ? ch.y : ch.x;
+    const int32_t far_ref = left_first ? ch.y : ch.x;
+    if (sp < B200_STACK) stack[sp++] = far_ref;
+    prefetch_ref(S, far_ref, false);
     return left_first ? ch.x : ch.y;
   }
   return hl ? ch.x : (hr ? ch.y : B200_DONE);
@@ -162,9 +178,9 @@ DEV int32_t node_step4(const DevScene &S, int32_t cur, const RaySetup &rs, float
   cswap4(k0, c0, k2, c2);
   cswap4(k1, c1, k3, c3);
   cswap4(k1, c1, k2, c2);
-  if (k3 < INF32 && sp < B200_STACK) stack[sp++] = c3;
-  if (k2 < INF32 && sp < B200_STACK) stack[sp++] = c2;
-  if (k1 < INF32 && sp < B200_STACK) stack[sp++] = c1;
+  if (k3 < INF32 && sp < B200_STACK) stack[sp++] = c3, prefetch_ref(S, c3, true);
+  if (k2 < INF32 && sp < B200_STACK) stack[sp++] = c2, prefetch_ref(S, c2, true);
+  if (k1 < INF32 && sp < B200_STACK) stack[sp++] = c1, prefetch_ref(S, c1, true);
   return k0 < INF32 ? c0 : B200_DONE;
 }
 
