@@ -155,6 +155,10 @@ def run_ours(args):
         ctx.set_option(abi.OPT_EXTEND_BLOCKS, args.extend_blocks)
     if args.no_fuse_miss:
         ctx.set_option(abi.OPT_FUSE_MISS, 0)
+    if args.pipelines:
+        ctx.set_option(abi.OPT_PIPELINES, args.pipelines)
+    if args.pctas:
+        ctx.set_option(abi.OPT_PIPE_EXTEND_CTAS, args.pctas)
     ctx.upload_scene(scene)
     ctx.set_camera(cam)
     accum = torch.zeros(H * W * 3, dtype=torch.float64, device="cuda")
@@ -185,8 +189,13 @@ def run_ours(args):
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
     clocks = sampler.stop() if sampler else None
     # per-kernel accounting from one extra, instrumented step (events around every k_extend launch)
+    st_all = step(want_stats=True)  # as configured: rays, samples, launches of one timed step
+    fence()
+    ctx.set_option(abi.OPT_PIPELINES, 1)  # then the extend kernel timed alone: with two pipelines the halves' kernels overlap
+    ctx.set_option(abi.OPT_WAVE_PATHS, max(1024, args.wave // 2))
     st = step(want_stats=True)
     fence()
+    st["kernel_launches"] = st_all["kernel_launches"]
     counts = torch.tensor([st["samples"], st["rays"], st["kernel_launches"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -200,6 +209,10 @@ def run_ours(args):
         out = torch.empty((H, W, 3), dtype=torch.float64, pin_memory=True).numpy()
         ctx2 = pkg.backend.Context(local)
         ctx2.set_option(abi.OPT_WAVE_PATHS, args.wave)
+        if args.pipelines:
+            ctx2.set_option(abi.OPT_PIPELINES, args.pipelines)
+        if args.pctas:
+            ctx2.set_option(abi.OPT_PIPE_EXTEND_CTAS, args.pctas)
 
         def e2e_step():
             ctx2.upload_scene(scene)
@@ -227,14 +240,14 @@ def run_ours(args):
         line = {"metric": METRIC, "value": rays * args.steps / (ms / 1e3) / 1e6, "unit": UNIT, "msamples_per_s": samples * args.steps / (ms / 1e3) / 1e6,
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "spp_per_gpu": spp, "wave_paths": args.wave, "seed": args.seed, "rays_per_sample": rays / samples,
-                           "l2": "inputs larger than L2: the wavefront state streamed per wave (16 Mi paths x 128 B = 2 GB) exceeds the 126 MB L2; the scene (~100 kB) is meant to stay cached",
+                "config": {"workload": WORKLOAD, "spp_per_gpu": spp, "wave_paths": args.wave, "pipelines": args.pipelines or 2, "seed": args.seed, "rays_per_sample": rays / samples,
+                           "l2": "inputs larger than L2: the wavefront state streamed per wave (16 Mi paths x 128 B = 2 GB per pipeline) exceeds the 126 MB L2; the scene (~100 kB) is meant to stay cached",
                            "parallelism": f"sample-range split x{world}, NCCL reduce of the fp64 accumulators" if world > 1 else "single GPU"},
                 "roofline": {"bound": "hbm", "kernel": "k_extend_persistent", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": TRAFFIC_BYTES_PER_RAY * st["rays"] / max(1, st["waves"]), "peak_source": peak_src, "bytes_per_ray": EXTEND_BYTES_PER_RAY,
                              "extend_share_of_step": st["extend_ms"] / st["gpu_ms"],
                              "algorithmic_bytes_per_launch": st["rays"] * EXTEND_BYTES_PER_RAY / max(1, st["waves"]), "launches": st["waves"],
-                             "note": "issue/latency bound, not HBM bound (fp32 box filter + binary64 reference-order leaf tests over an L1/L2-resident BVH); "
+                             "measured": "extend launches of one extra single-pipeline step (16 Mi-path waves), CUDA events around every launch", "note": "issue/latency bound, not HBM bound (fp32 box filter + binary64 reference-order leaf tests over an L1/L2-resident BVH); "
                                      "traffic = dram read+write per ray of a full launch from profiles/r01_p_extend_ncu_full.txt (ncu --set full) x mean rays per launch; see DESIGN.md"},
                 "e2e": e2e, "gpu_launches": int(launches * args.steps), "clocks": clocks}
         if world == 1 and not args.no_cpu:
@@ -252,11 +265,13 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step (default: the config's 500)")
-    ap.add_argument("--wave", type=int, default=1 << 24, help="paths resident per wave")
+    ap.add_argument("--wave", type=int, default=1 << 25, help="paths resident per wave, shared by the pipelines")
     ap.add_argument("--seed", type=int, default=0x5EED)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--refill", type=int, default=0, help="tuning: idle lanes per warp that trigger a ray fetch in the persistent extend kernel")
     ap.add_argument("--extend-blocks", type=int, default=0, help="tuning: CTAs/SM of the persistent extend kernel (4, 5, 6, 8)")
+    ap.add_argument("--pipelines", type=int, default=0, help="tuning: 1 or 2 independent wavefronts (two streams)")
+    ap.add_argument("--pctas", type=int, default=0, help="tuning: extend CTAs per SM in two-pipeline mode")
     ap.add_argument("--no-fuse-miss", action="store_true", help="tuning: send missing rays through the miss queue and its shade launch")
     ap.add_argument("--leaf", type=int, default=0, help="tuning: max primitives per BVH leaf")
     a = ap.parse_args()

@@ -58,7 +58,7 @@ struct b200rt_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // options
   int traversal = B200RT_TRAVERSAL_FAST;
-  uint32_t wave_paths = 1u << 24;
+  uint32_t wave_paths = 1u << 25; // shared by the pipelines: 2 x 16 Mi paths = 10 GB of wavefront state
   int kill_zero = 1;
   int bvh_leaf = 0;     // 0 = by scene size (profiles/r01_g_tune.txt): 1 primitive per leaf up to 8192 primitives, else 2
   int refill_lanes = 0; // 0 = by BVH size: fixed 32-ray batches for cache-resident trees, refill at 8 idle lanes from 32 Ki nodes
@@ -80,16 +80,23 @@ struct b200rt_ctx {
   uint32_t kinds_present = 0; // bit k: some material of the scene has b200rt_material_kind k (queues of absent kinds stay empty)
   // camera
   b200rt_camera cam{};
-  // wavefront pools
-  DevMem wave_mem;
-  uint32_t wave_capacity = 0;
-  bool wave_mirror = false;
-  PathBuf pool[2]{};
-  HitRef *hits = nullptr;
-  Rec *recs = nullptr;
-  Queues queues{};
-  WaveCtl *ctl = nullptr;
-  WaveCtl *h_ctl = nullptr; // pinned
+  // wavefront state: one set per pipeline (B200RT_OPT_PIPELINES; set 1 is only allocated for two pipelines)
+  struct WaveSet {
+    DevMem mem;
+    uint32_t capacity = 0;
+    bool mirror = false;
+    PathBuf pool[2]{};
+    HitRef *hits = nullptr;
+    Rec *recs = nullptr;
+    Queues queues{};
+    WaveCtl *ctl = nullptr;
+    WaveCtl *h_ctl = nullptr; // pinned
+    cudaStream_t stream = nullptr; // pipeline stream (two-pipeline mode)
+    cudaEvent_t done = nullptr;
+  } w[2];
+  cudaEvent_t ev_fork = nullptr;
+  int pipelines = 2;        // measured: +4 % on RTOW, +5 % on the Sponza stand-in over one pipeline (profiles/r01_r_pipelines.txt)
+  int pipe_extend_ctas = 4; // fewer (leaving registers for the other half's kernels) is slower: extend needs its occupancy
   double *accum = nullptr;  // W*H*3, used by b200rt_render
   size_t accum_elems = 0;
 };
@@ -264,7 +271,12 @@ int b200rt_create(int device, b200rt_ctx **out) {
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(cudaEventCreate(&c->ev0));
   CU(cudaEventCreate(&c->ev1));
-  CU(cudaMallocHost(&c->h_ctl, sizeof(WaveCtl)));
+  CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  for (auto &w : c->w) {
+    CU(cudaMallocHost(&w.h_ctl, sizeof(WaveCtl)));
+    CU(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&w.done, cudaEventDisableTiming));
+  }
   *out = c.release();
   return B200RT_OK;
 }
@@ -274,8 +286,14 @@ int b200rt_destroy(b200rt_ctx *c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   c->scene_mem.release();
-  c->wave_mem.release();
-  if (c->h_ctl) cudaFreeHost(c->h_ctl);
+  for (auto &w : c->w) {
+    if (w.stream) cudaStreamSynchronize(w.stream);
+    w.mem.release();
+    if (w.h_ctl) cudaFreeHost(w.h_ctl);
+    if (w.done) cudaEventDestroy(w.done);
+    if (w.stream) cudaStreamDestroy(w.stream);
+  }
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -303,6 +321,14 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
   case B200RT_OPT_EXTEND_BLOCKS: c->extend_blocks = (int)value; return B200RT_OK;
   case B200RT_OPT_SPECULATIVE_LEAF: c->speculative = value != 0; return B200RT_OK;
   case B200RT_OPT_FUSE_MISS: c->fuse_miss = value != 0; return B200RT_OK;
+  case B200RT_OPT_PIPELINES:
+    if (value != 1 && value != 2) return fail(B200RT_ERR_INVALID, "pipelines must be 1 or 2");
+    c->pipelines = (int)value;
+    return B200RT_OK;
+  case B200RT_OPT_PIPE_EXTEND_CTAS:
+    if (!(value >= 1 && value <= 4)) return fail(B200RT_ERR_INVALID, "extend CTAs per SM in two-pipeline mode must be in [1, 4]");
+    c->pipe_extend_ctas = (int)value;
+    return B200RT_OK;
   case B200RT_OPT_BVH_WIDTH:
     if (value != 0 && value != 2 && value != 4) return fail(B200RT_ERR_INVALID, "BVH width must be 0 (automatic), 2 or 4");
     c->bvh_width = (int)value; // takes effect at the next b200rt_upload_scene
@@ -573,40 +599,40 @@ int b200rt_generate_rays(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
 
 namespace {
 
-int ensure_wave(b200rt_ctx *c, uint32_t capacity, bool mirror) {
-  if (c->wave_capacity >= capacity && (!mirror || c->wave_mirror)) return B200RT_OK;
-  c->wave_mem.release();
-  c->wave_capacity = 0;
-  auto col = [&](void **p, size_t elem) { return c->wave_mem.alloc(p, (size_t)capacity * elem); };
+int ensure_wave(b200rt_ctx::WaveSet &w, uint32_t capacity, bool mirror) {
+  if (w.capacity >= capacity && (!mirror || w.mirror)) return B200RT_OK;
+  w.mem.release();
+  w.capacity = 0;
+  auto col = [&](void **p, size_t elem) { return w.mem.alloc(p, (size_t)capacity * elem); };
   for (int b = 0; b < 2; b++) {
-    CU(col((void **)&c->pool[b].base, B200_PATH_QUADS * sizeof(double2)));
-    c->pool[b].capacity = capacity;
+    CU(col((void **)&w.pool[b].base, B200_PATH_QUADS * sizeof(double2)));
+    w.pool[b].capacity = capacity;
   }
-  CU(col((void **)&c->hits, sizeof(HitRef)));
-  c->recs = nullptr;
-  if (mirror) CU(col((void **)&c->recs, sizeof(Rec)));
-  for (int k = 0; k < B200_NQUEUES; k++) CU(col((void **)&c->queues.q[k], 4));
-  CU(c->wave_mem.alloc((void **)&c->ctl, sizeof(WaveCtl)));
-  c->wave_capacity = capacity;
-  c->wave_mirror = mirror;
+  CU(col((void **)&w.hits, sizeof(HitRef)));
+  w.recs = nullptr;
+  if (mirror) CU(col((void **)&w.recs, sizeof(Rec)));
+  for (int k = 0; k < B200_NQUEUES; k++) CU(col((void **)&w.queues.q[k], 4));
+  CU(w.mem.alloc((void **)&w.ctl, sizeof(WaveCtl)));
+  w.capacity = capacity;
+  w.mirror = mirror;
   return B200RT_OK;
 }
 
-// one launch per queue that can be non-empty in this scene; returns the number of launches
 // Persistent extend launch.  The shared-memory carve-out is requested explicitly (smallest configuration that holds the
 // resident CTAs): what is left of the 256 KB is the L1 that caches BVH nodes and primitives.
-template <class K> void launch_extend(K kernel, b200rt_ctx *c, int ctas_per_sm, int threads, int smem_per_cta, cudaStream_t s, const PathBuf &cur, const WaveParams &wp) {
+template <class K>
+void launch_extend(K kernel, b200rt_ctx *c, b200rt_ctx::WaveSet &w, int ctas_per_sm, int threads, int smem_per_cta, cudaStream_t s, const PathBuf &cur, const WaveParams &wp) {
   const int want_kb = (ctas_per_sm * (smem_per_cta + 1024) + 1023) / 1024;
   cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, c->carveout_pct >= 0 ? c->carveout_pct : std::min(100, (want_kb * 100 + 227) / 228));
-  kernel<<<c->sm_count * ctas_per_sm, threads, 0, s>>>(c->ctl, c->S, cur, c->hits, wp);
+  kernel<<<c->sm_count * ctas_per_sm, threads, 0, s>>>(w.ctl, c->S, cur, w.hits, wp);
 }
 
 template <bool MIRROR>
-int launch_shades(b200rt_ctx *c, cudaStream_t s, int grid, const PathBuf &cur, const PathBuf &nxt, double *accum, const WaveParams &wp) {
+int launch_shades(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, int grid, const PathBuf &cur, const PathBuf &nxt, double *accum, const WaveParams &wp) {
   int n = 0;
 #define SHADE(K)                                                                                                       \
   if (K == B200_Q_MISS ? wp.fused_miss == 0 : (c->kinds_present >> K & 1u))                                                                \
-  n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(c->ctl, c->S, cur, nxt, c->hits, c->recs, c->queues.q[K], accum, wp)
+  n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(w.ctl, c->S, cur, nxt, w.hits, w.recs, w.queues.q[K], accum, wp)
   SHADE(B200_Q_MISS);
   SHADE(B200RT_MAT_DIFFUSE_LIGHT);
   SHADE(B200RT_MAT_LAMBERTIAN);
@@ -616,6 +642,52 @@ int launch_shades(b200rt_ctx *c, cudaStream_t s, int grid, const PathBuf &cur, c
   SHADE(B200RT_MAT_ISOTROPIC);
 #undef SHADE
   return n;
+}
+
+// One wave of one pipeline on stream s: generate -> extend -> classify -> shade per queue -> roll the counters over.
+// Returns the number of launches (negative: error).  ext_ctas = resident extend CTAs per SM (4 alone; fewer when a second
+// pipeline's shade kernels are meant to run beside it).  ext_events (may be NULL) receives an event pair around extend.
+int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned long long wave, const DevCamera &cam, const WaveParams &wp, int g_gen, int g_ext,
+                double *d_rgb_sum, int ext_ctas, std::vector<cudaEvent_t> *ext_events) {
+  const bool mirror = c->traversal == B200RT_TRAVERSAL_MIRROR;
+  const PathBuf &cur = w.pool[wave & 1], &nxt = w.pool[(wave & 1) ^ 1];
+  k_generate<<<g_gen, 256, 0, s>>>(w.ctl, cur, cam, wp, &w.ctl->nan_samples);
+  k_ctl_generated<<<1, 1, 0, s>>>(w.ctl);
+  if (ext_events) {
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a));
+    CU(cudaEventCreate(&b));
+    ext_events->push_back(a);
+    ext_events->push_back(b);
+    CU(cudaEventRecord(a, s));
+  }
+  if (mirror)
+    k_extend<true><<<g_ext, 128, 0, s>>>(w.ctl, c->S, cur, w.hits, w.recs, w.queues, wp);
+  else
+    switch (c->extend_blocks * 2 + (c->speculative ? 1 : 0)) {
+    // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
+#define EXT(MAXREG, SPEC, WARPS, STAGES)                                                                               \
+  launch_extend(k_extend_persistent<MAXREG, SPEC, WARPS, STAGES, false>, c, w, 65536 / (MAXREG * WARPS * 32), WARPS * 32, WARPS * STAGES * 3584, s, cur, wp)
+    case 12: EXT(80, false, 4, 1); break;  // 24 warps per SM
+    case 10: EXT(96, false, 2, 1); break;  // 20 warps
+    case 18: EXT(112, false, 2, 1); break; // 18 warps (option value 9: 2-warp CTAs)
+    case 34: EXT(120, false, 1, 1); break; // 17 warps (option value 17: 1-warp CTAs)
+    case 9: EXT(128, true, 4, 2); break;
+#undef EXT
+    default: // 128 registers, 4-warp CTAs
+      if (c->S.bvh4)
+        launch_extend(k_extend_persistent<128, false, 4, 2, true>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);
+      else if (c->extend_stages == 1 && wp.refill == 32)
+        launch_extend(k_extend_persistent<128, false, 4, 1, false>, c, w, ext_ctas, 128, 4 * 1 * 3584, s, cur, wp);
+      else
+        launch_extend(k_extend_persistent<128, false, 4, 2, false>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);
+      break;
+    }
+  if (ext_events) CU(cudaEventRecord(ext_events->back(), s));
+  if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(w.ctl, w.hits, w.queues);
+  const int n_shade = mirror ? launch_shades<true>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp) : launch_shades<false>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp);
+  k_ctl_swap<<<1, 1, 0, s>>>(w.ctl);
+  return (mirror ? 4 : 5) + n_shade;
 }
 
 } // namespace
@@ -634,81 +706,91 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   if (stats) std::memset(stats, 0, sizeof *stats);
   if (total == 0) return B200RT_OK;
   const bool mirror = c->traversal == B200RT_TRAVERSAL_MIRROR;
-  uint32_t capacity = c->wave_paths;
-  if (total < capacity) capacity = (uint32_t)((total + 31) & ~31ull);
-  int rc = ensure_wave(c, capacity, mirror);
-  if (rc != B200RT_OK) return rc;
+  // Two pipelines: the sample range is split in two halves that run as independent wavefronts on two streams, so that one
+  // half's kernels fill the SMs that the other half's kernel has already drained (every launch ends with a tail of
+  // partly idle SMs; the persistent extend kernel most of all).  pipe_extend_ctas < 4 would leave registers for the other
+  // half's shade kernels to run BESIDE extend; measured slower (extend needs its occupancy), so the default is 4.
+  const int n_pipe = (c->pipelines == 2 && !mirror && spp_end - spp_begin >= 2 && total >= (1ull << 21)) ? 2 : 1;
+  int rc;
   if (mirror && (rc = prepare_mirror(c)) != B200RT_OK) return rc;
-  capacity = c->wave_capacity; // a larger pool from an earlier call is kept; use min(wave_paths, pool)
-  if (capacity > c->wave_paths) capacity = c->wave_paths;
 
-  WaveParams wp;
-  wp.seed = seed;
-  wp.npix = npix;
-  wp.width = (uint32_t)c->cam.image_width;
-  wp.spp_begin = spp_begin;
-  wp.max_depth = c->cam.max_depth;
-  wp.kill_zero = c->kill_zero;
-  wp.fused_miss = (mirror || !c->fuse_miss) ? 0 : c->bg_mode;
-  wp.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 8 : 32);
-  for (int k = 0; k < 3; k++) wp.bound[k] = c->S.bound[k];
+  WaveParams wp[2];
+  unsigned long long tot[2] = {total, 0};
+  uint32_t cap[2] = {0, 0};
+  const int mid = n_pipe == 2 ? spp_begin + (spp_end - spp_begin) / 2 : spp_end;
+  for (int p = 0; p < n_pipe; p++) {
+    WaveParams &q = wp[p];
+    q.seed = seed;
+    q.npix = npix;
+    q.width = (uint32_t)c->cam.image_width;
+    q.spp_begin = p == 0 ? spp_begin : mid;
+    q.max_depth = c->cam.max_depth;
+    q.kill_zero = c->kill_zero;
+    q.fused_miss = (mirror || !c->fuse_miss) ? 0 : c->bg_mode;
+    q.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 8 : 32);
+    for (int k = 0; k < 3; k++) q.bound[k] = c->S.bound[k];
+    tot[p] = (unsigned long long)npix * (unsigned long long)(p == 0 ? mid - spp_begin : spp_end - mid);
+    uint32_t capacity = c->wave_paths / (uint32_t)n_pipe;
+    if (tot[p] < capacity) capacity = (uint32_t)((tot[p] + 31) & ~31ull);
+    if ((rc = ensure_wave(c->w[p], capacity, mirror)) != B200RT_OK) return rc;
+    capacity = c->w[p].capacity; // a larger pool from an earlier call is kept; use min(wave_paths share, pool)
+    if (capacity > c->wave_paths / (uint32_t)n_pipe) capacity = c->wave_paths / (uint32_t)n_pipe;
+    cap[p] = capacity;
+  }
   const DevCamera cam = make_camera(c->cam);
-  const int g_gen = grid_for(c, capacity, 256, 8), g_ext = grid_for(c, capacity, 128, 16);
+  const int ext_ctas = n_pipe == 2 ? c->pipe_extend_ctas : 4;
+  cudaStream_t ps[2] = {s, s};
+  if (n_pipe == 2) {
+    CU(cudaEventRecord(c->ev_fork, s));
+    for (int p = 0; p < 2; p++) {
+      ps[p] = c->w[p].stream;
+      CU(cudaStreamWaitEvent(ps[p], c->ev_fork, 0));
+    }
+  }
 
   std::vector<cudaEvent_t> ext_events;
   if (stats) CU(cudaEventRecord(c->ev0, s));
-  k_ctl_init<<<1, 1, 0, s>>>(c->ctl, total, capacity);
-  unsigned long long launches = 1, wave = 0, next_check = (total + capacity - 1) / capacity;
+  unsigned long long launches = 0, wave = 0, next_check = 0;
+  bool done[2] = {false, n_pipe == 1};
+  for (int p = 0; p < n_pipe; p++) {
+    k_ctl_init<<<1, 1, 0, ps[p]>>>(c->w[p].ctl, tot[p], cap[p]);
+    launches++;
+    next_check = std::max(next_check, (tot[p] + cap[p] - 1) / cap[p]);
+  }
   for (;;) {
-    const PathBuf &cur = c->pool[wave & 1], &nxt = c->pool[(wave & 1) ^ 1];
-    k_generate<<<g_gen, 256, 0, s>>>(c->ctl, cur, cam, wp, &c->ctl->nan_samples);
-    k_ctl_generated<<<1, 1, 0, s>>>(c->ctl);
-    if (stats) {
-      cudaEvent_t a, b;
-      CU(cudaEventCreate(&a));
-      CU(cudaEventCreate(&b));
-      ext_events.push_back(a);
-      ext_events.push_back(b);
-      CU(cudaEventRecord(a, s));
+    for (int p = 0; p < n_pipe; p++) {
+      if (done[p]) continue;
+      const int n = launch_wave(c, c->w[p], ps[p], wave, cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas,
+                                stats && n_pipe == 1 ? &ext_events : nullptr);
+      if (n < 0) return n;
+      launches += (unsigned long long)n;
     }
-    if (mirror)
-      k_extend<true><<<g_ext, 128, 0, s>>>(c->ctl, c->S, cur, c->hits, c->recs, c->queues, wp);
-    else
-      switch (c->extend_blocks * 2 + (c->speculative ? 1 : 0)) {
-      // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
-#define EXT(MAXREG, SPEC, WARPS, STAGES)                                                                               \
-  launch_extend(k_extend_persistent<MAXREG, SPEC, WARPS, STAGES, false>, c, 65536 / (MAXREG * WARPS * 32), WARPS * 32, WARPS * STAGES * 3584, s, cur, wp)
-      case 12: EXT(80, false, 4, 1); break;  // 24 warps per SM
-      case 10: EXT(96, false, 2, 1); break;  // 20 warps
-      case 18: EXT(112, false, 2, 1); break; // 18 warps (option value 9: 2-warp CTAs)
-      case 34: EXT(120, false, 1, 1); break; // 17 warps (option value 17: 1-warp CTAs)
-      case 9: EXT(128, true, 4, 2); break;
-      default:
-        if (c->S.bvh4)
-          launch_extend(k_extend_persistent<128, false, 4, 2, true>, c, 4, 128, 4 * 2 * 3584, s, cur, wp);
-        else if (c->extend_stages == 1 && wp.refill == 32)
-          EXT(128, false, 4, 1);
-        else
-          EXT(128, false, 4, 2);
-        break; // 16 warps
-#undef EXT
-      }
-    if (stats) CU(cudaEventRecord(ext_events.back(), s));
-    if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(c->ctl, c->hits, c->queues);
-    const int n_shade = mirror ? launch_shades<true>(c, s, g_ext, cur, nxt, d_rgb_sum, wp) : launch_shades<false>(c, s, g_ext, cur, nxt, d_rgb_sum, wp);
-    k_ctl_swap<<<1, 1, 0, s>>>(c->ctl);
-    launches += (mirror ? 4 : 5) + n_shade;
     wave++;
     if (wave >= next_check) {
-      CU(cudaMemcpyAsync(c->h_ctl, c->ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, s));
-      CU(cudaStreamSynchronize(s));
-      const WaveCtl &h = *c->h_ctl;
-      if (h.n_cur == 0 && h.next_sample >= h.total_samples) break;
-      const unsigned long long left = h.total_samples - h.next_sample;
-      next_check = wave + (left > 0 ? std::max<unsigned long long>(1, left / capacity) : 2);
+      for (int p = 0; p < n_pipe; p++)
+        if (!done[p]) CU(cudaMemcpyAsync(c->w[p].h_ctl, c->w[p].ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, ps[p]));
+      unsigned long long ahead = 2;
+      for (int p = 0; p < n_pipe; p++) {
+        if (done[p]) continue;
+        CU(cudaStreamSynchronize(ps[p]));
+        const WaveCtl &h = *c->w[p].h_ctl;
+        if (h.n_cur == 0 && h.next_sample >= h.total_samples) {
+          done[p] = true;
+          continue;
+        }
+        const unsigned long long left = h.total_samples - h.next_sample;
+        if (left > 0) ahead = std::max(ahead, std::max<unsigned long long>(1, left / cap[p]));
+      }
+      if (done[0] && done[1]) break;
+      next_check = wave + ahead;
     }
   }
   CU(cudaGetLastError());
+  if (n_pipe == 2) // the caller's stream continues when both halves are in the accumulator
+    for (int p = 0; p < 2; p++) {
+      CU(cudaEventRecord(c->w[p].done, ps[p]));
+      CU(cudaStreamWaitEvent(s, c->w[p].done, 0));
+    }
   if (stats) {
     CU(cudaEventRecord(c->ev1, s));
     CU(cudaEventSynchronize(c->ev1));
@@ -722,10 +804,9 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
       ext += e;
     }
     for (cudaEvent_t e : ext_events) cudaEventDestroy(e);
-    stats->extend_ms = ext;
+    stats->extend_ms = ext; // not measured with two pipelines (the kernels of the halves overlap)
     stats->samples = total;
-    stats->rays = c->h_ctl->rays;
-    stats->nan_samples = c->h_ctl->nan_samples;
+    for (int p = 0; p < n_pipe; p++) stats->rays += c->w[p].h_ctl->rays, stats->nan_samples += c->w[p].h_ctl->nan_samples;
     stats->kernel_launches = launches;
     stats->waves = wave;
   }

@@ -216,7 +216,7 @@ typedef struct b200rt_camera {
 /* ------------------------------------------------------------------ options */
 typedef enum b200rt_option {
   B200RT_OPT_TRAVERSAL = 0,     /* 0 = compacted SAH BVH (default), 1 = node-for-node mirror of the reference graph */
-  B200RT_OPT_WAVE_PATHS = 1,    /* paths resident per wave (default 16 Mi = 5 GB of wavefront state) */
+  B200RT_OPT_WAVE_PATHS = 1,    /* paths resident per wave, shared by the pipelines (default 32 Mi = 10 GB of wavefront state) */
   B200RT_OPT_KILL_ZERO_WEIGHT = 2, /* 1 (default): drop paths whose throughput is exactly 0 in all channels */
   B200RT_OPT_BVH_LEAF_SIZE = 3, /* max primitives per leaf of the compacted BVH; 0 (default) = 1 up to 8192 primitives, else 2 */
   B200RT_OPT_SMEM_NODES = 4,    /* top-of-tree nodes staged in shared memory (reserved) */
@@ -227,6 +227,8 @@ typedef enum b200rt_option {
   B200RT_OPT_SMEM_CARVEOUT = 10, /* tuning: shared-memory carve-out of the extend kernel in percent, -1 (default) = smallest that fits */
   B200RT_OPT_BVH_BUILDER = 11,  /* who builds the compacted BVH that replaces bvh_node's constructor (src/bvh_node.h:18-47): B200RT_BVH_HOST_SAH (default) or B200RT_BVH_DEVICE_LBVH */
   B200RT_OPT_BVH_WIDTH = 12,    /* children per node of the traversed tree: 2, 4 (collapsed from the host SAH BVH2), 0 (default) = 4 above 2048 primitives */
+  B200RT_OPT_PIPELINES = 13,    /* 1 or 2 (default): with 2 the sample range is split into two independent wavefronts on two streams; each half's kernels fill the SMs the other half's kernel has drained */
+  B200RT_OPT_PIPE_EXTEND_CTAS = 14, /* tuning: resident extend CTAs per SM in two-pipeline mode (1..4, default 4; fewer leave registers for the other half's kernels and were measured slower) */
   B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 8 from 32 Ki BVH nodes) */
 } b200rt_option;
 

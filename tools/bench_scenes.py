@@ -74,11 +74,13 @@ def main():
     ap.add_argument("--cpu", action="store_true", help="add the CPU baseline of every scene (see cpu_baseline)")
     ap.add_argument("--builder", type=int, default=0, help="0 = host SAH BVH (default), 1 = device LBVH (csrc/bvh_gpu.cuh)")
     ap.add_argument("--width", type=int, default=0, help="BVH width: 0 = automatic, 2, 4")
+    ap.add_argument("--pipelines", type=int, default=2, help="independent wavefronts on two streams (1 also reports the extend share)")
     ap.add_argument("--mirror", action="store_true", help="also time the node-for-node mirror traversal (parity arbiter)")
     args = ap.parse_args()
     ctx = pkg.backend.Context(0)
     ctx.set_option(abi.OPT_BVH_BUILDER, args.builder)
     ctx.set_option(abi.OPT_BVH_WIDTH, args.width)
+    ctx.set_option(abi.OPT_PIPELINES, args.pipelines)
     for name in args.scenes.split(","):
         t0 = time.perf_counter()
         sc, cam = load(name)
@@ -99,7 +101,7 @@ def main():
         line = {"scene": name, "builder": "device LBVH" if args.builder else "host SAH", "config": CONFIGS[name], "width": cam.image_width, "height": cam.image_height, "spp_timed": spp,
                 "spp_config": cam.samples_per_pixel, "max_depth": cam.max_depth, "mrays_per_s": best["rays"] / best["gpu_ms"] / 1e3,
                 "msamples_per_s": best["samples"] / best["gpu_ms"] / 1e3, "rays_per_sample": best["rays"] / best["samples"],
-                "gpu_ms": best["gpu_ms"], "extend_share": best["extend_ms"] / best["gpu_ms"], "waves": best["waves"],
+                "gpu_ms": best["gpu_ms"], "extend_share": (best["extend_ms"] / best["gpu_ms"]) if best["extend_ms"] > 0 else None, "waves": best["waves"],
                 "kernel_launches": best["kernel_launches"], "nan_samples": best["nan_samples"],
                 "bvh": {k: info[k] for k in ("n_nodes", "n_leaves", "n_prims", "max_depth", "build_ms", "sah_cost")},
                 "scene_load_s": t_load, "upload_s": t_up,

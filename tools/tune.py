@@ -39,6 +39,8 @@ def main():
     ap.add_argument("--leaf", default="0")
     ap.add_argument("--stages", default="1", help="ray batches staged per warp: 1, 2 or 1,2")
     ap.add_argument("--carveout", default="-1", help="shared-memory carve-out percent of the extend kernel (-1 = automatic)")
+    ap.add_argument("--pipelines", default="1", help="1, 2 or 1,2: independent wavefronts on two streams")
+    ap.add_argument("--pctas", default="3", help="extend CTAs per SM in two-pipeline mode")
     ap.add_argument("--width", type=int, default=0, help="BVH width: 0 = automatic, 2, 4")
     ap.add_argument("--spec", default="0", help="speculative (postponed-leaf) traversal: 0, 1 or 0,1")
     a = ap.parse_args()
@@ -52,8 +54,12 @@ def main():
         ctx.set_option(abi.OPT_BVH_WIDTH, a.width)
         ctx.upload_scene(scene)
         ctx.set_camera(cam)
-        for wave, refill, blocks, spec, stages, carve in itertools.product(ints(a.wave), ints(a.refill), ints(a.blocks), ints(a.spec), ints(a.stages),
-                                                                           ints(a.carveout)):
+        for wave, refill, blocks, spec, stages, carve, pipes, pctas in itertools.product(ints(a.wave), ints(a.refill), ints(a.blocks), ints(a.spec), ints(a.stages),
+                                                                                         ints(a.carveout), ints(a.pipelines), ints(a.pctas)):
+            if pipes == 1 and pctas != ints(a.pctas)[0]:
+                continue
+            ctx.set_option(abi.OPT_PIPELINES, pipes)
+            ctx.set_option(abi.OPT_PIPE_EXTEND_CTAS, pctas)
             ctx.set_option(abi.OPT_SPECULATIVE_LEAF, spec)
             ctx.set_option(abi.OPT_EXTEND_STAGES, stages)
             ctx.set_option(abi.OPT_SMEM_CARVEOUT, carve)
@@ -66,7 +72,7 @@ def main():
                 st = ctx.render_device(0x5EED, 0, a.spp, accum.data_ptr(), stream, want_stats=True)
                 if best is None or st["gpu_ms"] < best["gpu_ms"]:
                     best = st
-            print(json.dumps({"scene": a.scene, "spp": a.spp, "leaf": leaf, "wave_log2": wave, "refill": refill, "blocks": blocks, "spec": spec, "width": a.width, "stages": stages, "carveout": carve,
+            print(json.dumps({"scene": a.scene, "spp": a.spp, "leaf": leaf, "wave_log2": wave, "refill": refill, "blocks": blocks, "spec": spec, "width": a.width, "pipelines": pipes, "pctas": pctas, "stages": stages, "carveout": carve,
                               "mrays_per_s": best["rays"] / best["gpu_ms"] / 1e3, "gpu_ms": best["gpu_ms"], "extend_ms": best["extend_ms"],
                               "waves": best["waves"]}), flush=True)
         ctx.close()
