@@ -51,6 +51,8 @@ struct DevMem { // owns device allocations of a context
 
 } // namespace
 
+#define B200_MAX_PIPELINES 4
+
 struct b200rt_ctx {
   int device = 0;
   int sm_count = 148;
@@ -93,7 +95,7 @@ struct b200rt_ctx {
     WaveCtl *h_ctl = nullptr; // pinned
     cudaStream_t stream = nullptr; // pipeline stream (two-pipeline mode)
     cudaEvent_t done = nullptr;
-  } w[2];
+  } w[B200_MAX_PIPELINES];
   cudaEvent_t ev_fork = nullptr;
   int pipelines = 2;        // measured: +4 % on RTOW, +5 % on the Sponza stand-in over one pipeline (profiles/r01_r_pipelines.txt)
   int pipe_extend_ctas = 4; // fewer (leaving registers for the other half's kernels) is slower: extend needs its occupancy
@@ -322,7 +324,7 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
   case B200RT_OPT_SPECULATIVE_LEAF: c->speculative = value != 0; return B200RT_OK;
   case B200RT_OPT_FUSE_MISS: c->fuse_miss = value != 0; return B200RT_OK;
   case B200RT_OPT_PIPELINES:
-    if (value != 1 && value != 2) return fail(B200RT_ERR_INVALID, "pipelines must be 1 or 2");
+    if (!(value >= 1 && value <= B200_MAX_PIPELINES)) return fail(B200RT_ERR_INVALID, "pipelines must be in [1, %d]", B200_MAX_PIPELINES);
     c->pipelines = (int)value;
     return B200RT_OK;
   case B200RT_OPT_PIPE_EXTEND_CTAS:
@@ -710,26 +712,28 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   // half's kernels fill the SMs that the other half's kernel has already drained (every launch ends with a tail of
   // partly idle SMs; the persistent extend kernel most of all).  pipe_extend_ctas < 4 would leave registers for the other
   // half's shade kernels to run BESIDE extend; measured slower (extend needs its occupancy), so the default is 4.
-  const int n_pipe = (c->pipelines == 2 && !mirror && spp_end - spp_begin >= 2 && total >= (1ull << 21)) ? 2 : 1;
+  int n_pipe = (c->pipelines > 1 && !mirror && total >= (1ull << 21)) ? std::min(c->pipelines, spp_end - spp_begin) : 1;
   int rc;
   if (mirror && (rc = prepare_mirror(c)) != B200RT_OK) return rc;
 
-  WaveParams wp[2];
-  unsigned long long tot[2] = {total, 0};
-  uint32_t cap[2] = {0, 0};
-  const int mid = n_pipe == 2 ? spp_begin + (spp_end - spp_begin) / 2 : spp_end;
+  WaveParams wp[B200_MAX_PIPELINES];
+  unsigned long long tot[B200_MAX_PIPELINES] = {0};
+  uint32_t cap[B200_MAX_PIPELINES] = {0};
   for (int p = 0; p < n_pipe; p++) {
+    // contiguous, disjoint, covering sample sub-ranges whose sizes differ by at most one
+    const int span = spp_end - spp_begin, base = span / n_pipe, extra = span % n_pipe;
+    const int lo = spp_begin + p * base + std::min(p, extra), hi = lo + base + (p < extra ? 1 : 0);
     WaveParams &q = wp[p];
     q.seed = seed;
     q.npix = npix;
     q.width = (uint32_t)c->cam.image_width;
-    q.spp_begin = p == 0 ? spp_begin : mid;
+    q.spp_begin = lo;
     q.max_depth = c->cam.max_depth;
     q.kill_zero = c->kill_zero;
     q.fused_miss = (mirror || !c->fuse_miss) ? 0 : c->bg_mode;
     q.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 8 : 32);
     for (int k = 0; k < 3; k++) q.bound[k] = c->S.bound[k];
-    tot[p] = (unsigned long long)npix * (unsigned long long)(p == 0 ? mid - spp_begin : spp_end - mid);
+    tot[p] = (unsigned long long)npix * (unsigned long long)(hi - lo);
     uint32_t capacity = c->wave_paths / (uint32_t)n_pipe;
     if (tot[p] < capacity) capacity = (uint32_t)((tot[p] + 31) & ~31ull);
     if ((rc = ensure_wave(c->w[p], capacity, mirror)) != B200RT_OK) return rc;
@@ -738,11 +742,11 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     cap[p] = capacity;
   }
   const DevCamera cam = make_camera(c->cam);
-  const int ext_ctas = n_pipe == 2 ? c->pipe_extend_ctas : 4;
-  cudaStream_t ps[2] = {s, s};
-  if (n_pipe == 2) {
+  const int ext_ctas = n_pipe > 1 ? c->pipe_extend_ctas : 4;
+  cudaStream_t ps[B200_MAX_PIPELINES] = {s, s, s, s};
+  if (n_pipe > 1) {
     CU(cudaEventRecord(c->ev_fork, s));
-    for (int p = 0; p < 2; p++) {
+    for (int p = 0; p < n_pipe; p++) {
       ps[p] = c->w[p].stream;
       CU(cudaStreamWaitEvent(ps[p], c->ev_fork, 0));
     }
@@ -751,7 +755,8 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   std::vector<cudaEvent_t> ext_events;
   if (stats) CU(cudaEventRecord(c->ev0, s));
   unsigned long long launches = 0, wave = 0, next_check = 0;
-  bool done[2] = {false, n_pipe == 1};
+  bool done[B200_MAX_PIPELINES];
+  for (int p = 0; p < B200_MAX_PIPELINES; p++) done[p] = p >= n_pipe;
   for (int p = 0; p < n_pipe; p++) {
     k_ctl_init<<<1, 1, 0, ps[p]>>>(c->w[p].ctl, tot[p], cap[p]);
     launches++;
@@ -781,13 +786,13 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
         const unsigned long long left = h.total_samples - h.next_sample;
         if (left > 0) ahead = std::max(ahead, std::max<unsigned long long>(1, left / cap[p]));
       }
-      if (done[0] && done[1]) break;
+      if (done[0] && done[1] && done[2] && done[3]) break;
       next_check = wave + ahead;
     }
   }
   CU(cudaGetLastError());
-  if (n_pipe == 2) // the caller's stream continues when both halves are in the accumulator
-    for (int p = 0; p < 2; p++) {
+  if (n_pipe > 1) // the caller's stream continues when every part is in the accumulator
+    for (int p = 0; p < n_pipe; p++) {
       CU(cudaEventRecord(c->w[p].done, ps[p]));
       CU(cudaStreamWaitEvent(s, c->w[p].done, 0));
     }

@@ -497,8 +497,8 @@ def test_two_pipelines_render_the_same_frame(name):
         c.set_camera(cam)
         c.set_option(abi.OPT_PIPELINES, 1)
         one, st1 = c.render(9, 3, 11)
-        for ctas in (4, 3, 2):
-            c.set_option(abi.OPT_PIPELINES, 2)
+        for ctas, npipe in ((4, 2), (3, 2), (2, 2), (4, 3), (4, 4)):
+            c.set_option(abi.OPT_PIPELINES, npipe)
             c.set_option(abi.OPT_PIPE_EXTEND_CTAS, ctas)
             two, st2 = c.render(9, 3, 11)
             assert st2["rays"] == st1["rays"] and st2["samples"] == st1["samples"]
