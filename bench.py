@@ -153,6 +153,8 @@ def run_ours(args):
         ctx.set_option(abi.OPT_BVH_LEAF_SIZE, args.leaf)
     if args.extend_blocks:
         ctx.set_option(abi.OPT_EXTEND_BLOCKS, args.extend_blocks)
+    if args.stages:
+        ctx.set_option(abi.OPT_EXTEND_STAGES, args.stages)
     if args.no_fuse_miss:
         ctx.set_option(abi.OPT_FUSE_MISS, 0)
     if args.pipelines:
@@ -213,6 +215,8 @@ def run_ours(args):
             ctx2.set_option(abi.OPT_PIPELINES, args.pipelines)
         if args.pctas:
             ctx2.set_option(abi.OPT_PIPE_EXTEND_CTAS, args.pctas)
+        if args.stages:
+            ctx2.set_option(abi.OPT_EXTEND_STAGES, args.stages)
 
         def e2e_step():
             ctx2.upload_scene(scene)
@@ -269,6 +273,7 @@ if __name__ == "__main__":
     ap.add_argument("--seed", type=int, default=0x5EED)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--refill", type=int, default=0, help="tuning: idle lanes per warp that trigger a ray fetch in the persistent extend kernel")
+    ap.add_argument("--stages", type=int, default=0, help="tuning: ray batches staged per warp in the extend kernel (1 or 2)")
     ap.add_argument("--extend-blocks", type=int, default=0, help="tuning: CTAs/SM of the persistent extend kernel (4, 5, 6, 8)")
     ap.add_argument("--pipelines", type=int, default=0, help="tuning: 1 or 2 independent wavefronts (two streams)")
     ap.add_argument("--pctas", type=int, default=0, help="tuning: extend CTAs per SM in two-pipeline mode")
