@@ -25,7 +25,7 @@ namespace b200 {
 
 struct WaveCtl {
   unsigned long long next_sample, total_samples, rays, nan_samples, waves, extend_rays_dummy;
-  uint32_t n_cur, n_next, capacity, fetch; // fetch: next unclaimed ray of the persistent extend kernel
+  uint32_t n_cur, n_next, capacity, fetch; // fetch: next unclaimed 32-ray batch of the persistent extend kernel
   uint32_t q_count[8];
 };
 
@@ -298,6 +298,9 @@ DEV void cp_async_wait_all() {
 // soon as its 32 rays have been taken into registers.  Shared memory is carved out of the L1 that caches the BVH, so the
 // smaller footprint (14 KB instead of 28 KB per CTA) is not free to give away: see DESIGN.md.
 // WIDE: the tree is the BVH4 of scene_dev.cuh (S.bvh4) instead of the BVH2.
+#ifndef B200_EXT_DYNAMIC
+#define B200_EXT_DYNAMIC 4 // largest number of batches claimed per atomic; 0 = static striding (profiles/r01_v_*)
+#endif
 template <int MAXREG, bool SPEC, int WARPS, int STAGES, bool WIDE>
 __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp) {
 #if B200_PATH_PAIRED
@@ -339,13 +342,47 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
   // here (counted, never queued) and the scene needs no miss launch at all.
   auto finish_miss = [&](uint32_t i) { store_hit(hits, i, 0.0, -1, wp.fused_miss ? B200_Q_MISS_DONE : B200_Q_MISS); };
 
+#if B200_EXT_DYNAMIC
+  // batches are CLAIMED (B200_EXT_DYNAMIC at a time, one atomic per claim) instead of strided: a warp that drew cheap rays
+  // takes more of them, which shortens the tail of the launch.  The atomic for the NEXT chunk is issued when the last batch
+  // of the current one is handed out, so its round trip is hidden behind a whole batch of traversal.
+  uint32_t cl_next = 0, cl_end = 0, cl_pending = 0;
+  uint32_t *const fetch = const_cast<uint32_t *>(&c->fetch);
+  // guided chunks: B200_EXT_DYNAMIC batches per claim while plenty remain (few atomics), shrinking to 1 over the last
+  // 2 * B200_EXT_DYNAMIC batches per warp (fine-grained tail).  `seen` may be stale: any chunk size is valid.
+  const uint32_t inv = 0xffffffffu / (2u * n_warps);
+  auto chunk_for = [&](uint32_t seen) -> uint32_t {
+    const uint32_t rem = seen < n_batches ? n_batches - seen : 0u;
+    return min((uint32_t)B200_EXT_DYNAMIC, max(1u, __umulhi(rem, inv)));
+  };
+  uint32_t cl_ch = chunk_for(0);
+  if (lane == 0) cl_pending = atomicAdd(fetch, cl_ch);
+  auto claim = [&]() -> uint32_t {
+    if (cl_next == cl_end) {
+      cl_next = __shfl_sync(FULL, cl_pending, 0);
+      cl_end = cl_next + cl_ch;
+    }
+    const uint32_t b = cl_next++;
+    if (cl_next == cl_end) {
+      cl_ch = chunk_for(cl_end);
+      if (lane == 0) cl_pending = atomicAdd(fetch, cl_ch);
+    }
+    return b;
+  };
+  uint32_t batch = claim(), batch_ahead = 0;
+#else
   uint32_t batch = blockIdx.x * WARPS + wib; // the batch staged in `stg`
+#endif
   int stg = 0;
   prefetch(0, batch);
   cp_async_wait_all();
   __syncwarp();
   uint32_t base = batch * 32, count = batch < n_batches ? min(32u, n - base) : 0u, taken = 0;
+#if B200_EXT_DYNAMIC
+  if (STAGES == 2) prefetch(1, batch_ahead = claim());
+#else
   if (STAGES == 2) prefetch(1, batch + n_warps);
+#endif
 
   bool active = false;
   uint32_t idx = 0;
@@ -364,12 +401,20 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
       while (idle != 0 && count > 0) {
         if (taken == count) { // next staged batch (already in flight)
           const int drained = stg;
+#if B200_EXT_DYNAMIC
+          batch = batch_ahead; // STAGES == 1: set when the prefetch was issued
+#else
           batch += n_warps;
+#endif
           if (STAGES == 2) stg ^= 1;
           cp_async_wait_all();
           __syncwarp();
           base = batch * 32, count = batch < n_batches ? min(32u, n - base) : 0u, taken = 0;
+#if B200_EXT_DYNAMIC
+          if (STAGES == 2) prefetch(drained, batch_ahead = claim());
+#else
           if (STAGES == 2) prefetch(drained, batch + n_warps); // refill the stage just drained
+#endif
           continue;
         }
         const uint32_t slot = taken + (uint32_t)__popc(idle & ((1u << lane) - 1u));
@@ -410,7 +455,11 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
         taken += min((uint32_t)__popc(idle), count - taken);
         if (STAGES == 1 && taken == count) { // every ray of the stage is in registers now: start fetching the next batch into it
           __syncwarp();
+#if B200_EXT_DYNAMIC
+          prefetch(0, batch_ahead = claim());
+#else
           prefetch(0, batch + n_warps);
+#endif
         }
         idle = __ballot_sync(FULL, !active);
       }
