@@ -653,8 +653,20 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
                 double *d_rgb_sum, int ext_ctas, std::vector<cudaEvent_t> *ext_events) {
   const bool mirror = c->traversal == B200RT_TRAVERSAL_MIRROR;
   const PathBuf &cur = w.pool[wave & 1], &nxt = w.pool[(wave & 1) ^ 1];
-  k_generate<<<g_gen, 256, 0, s>>>(w.ctl, cur, cam, wp, &w.ctl->nan_samples);
-  k_ctl_generated<<<1, 1, 0, s>>>(w.ctl);
+  const bool compact = cam.c.mode == B200RT_CAM_FISHEYE; // the only camera with samples that produce no ray
+  int n_gen_launches = 2;
+  if (compact) {
+    // dropped samples leave room in the wave: further passes top it up (each sees the n_cur / next_sample the last one left)
+    const int passes = 2; // 1: -2.7 % on Fox, 3: same as 2 (profiles/r01_x_fox_gen_passes.txt)
+    for (int k = 0; k < passes; k++) {
+      k_generate<true><<<g_gen, 256, 0, s>>>(w.ctl, cur, cam, wp);
+      k_ctl_generated<<<1, 1, 0, s>>>(w.ctl, 1);
+    }
+    n_gen_launches = 2 * passes;
+  } else {
+    k_generate<false><<<g_gen, 256, 0, s>>>(w.ctl, cur, cam, wp);
+    k_ctl_generated<<<1, 1, 0, s>>>(w.ctl, 0);
+  }
   if (ext_events) {
     cudaEvent_t a, b;
     CU(cudaEventCreate(&a));
@@ -689,7 +701,7 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
   if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(w.ctl, w.hits, w.queues);
   const int n_shade = mirror ? launch_shades<true>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp) : launch_shades<false>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp);
   k_ctl_swap<<<1, 1, 0, s>>>(w.ctl);
-  return (mirror ? 4 : 5) + n_shade;
+  return (mirror ? 2 : 3) + n_gen_launches + n_shade;
 }
 
 } // namespace

@@ -27,6 +27,7 @@ struct WaveCtl {
   unsigned long long next_sample, total_samples, rays, nan_samples, waves, extend_rays_dummy;
   uint32_t n_cur, n_next, capacity, fetch; // fetch: next unclaimed 32-ray batch of the persistent extend kernel
   uint32_t q_count[8];
+  uint32_t n_gen, pad; // n_gen: live paths appended by k_generate<COMPACT> in this wave
 };
 
 // Path state = eight 16-byte "quads" per path.  The fp32 box-filter constants (traverse.cuh) are computed by the PRODUCER
@@ -145,17 +146,19 @@ __global__ void k_ctl_init(WaveCtl *c, unsigned long long total, uint32_t capaci
   c->n_next = 0;
   c->capacity = capacity;
   c->fetch = 0;
+  c->n_gen = 0;
   for (int k = 0; k < 8; k++) c->q_count[k] = 0;
 }
 DEV uint32_t wave_refill(const WaveCtl *c) {
   const unsigned long long room = c->capacity - c->n_cur, left = c->total_samples - c->next_sample;
   return (uint32_t)(room < left ? room : left);
 }
-__global__ void k_ctl_generated(WaveCtl *c) {
+__global__ void k_ctl_generated(WaveCtl *c, int compact) {
   const uint32_t n = wave_refill(c);
-  c->n_cur += n;
+  c->n_cur += compact ? c->n_gen : n;
   c->next_sample += n;
   c->fetch = 0;
+  c->n_gen = 0;
 }
 __global__ void k_ctl_swap(WaveCtl *c) {
   unsigned long long r = 0;
@@ -167,19 +170,48 @@ __global__ void k_ctl_swap(WaveCtl *c) {
 }
 
 // ------------------------------------------------------------------------------------------------ generate
-__global__ void __launch_bounds__(256) k_generate(const WaveCtl *c, PathBuf cur, DevCamera cam, WaveParams wp, unsigned long long *nan_samples) {
+// COMPACT (fisheye cameras): samples outside the image circle produce no ray (NaN direction, src/camera.h:268-282) and add
+// exactly 0; they are counted and DROPPED here instead of riding through extend and classify as dead slots (56 % of the Fox
+// config's samples).  Live paths are appended behind n_cur with one atomic per CTA iteration; k_ctl_generated adds n_gen.
+template <bool COMPACT>
+__global__ void __launch_bounds__(256) k_generate(WaveCtl *c, PathBuf cur, DevCamera cam, WaveParams wp) {
   const uint32_t n_new = wave_refill(c), n_cur = c->n_cur;
   const unsigned long long g0 = c->next_sample;
-  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_new; idx += gridDim.x * blockDim.x) {
-    const unsigned long long g = g0 + idx;
-    const uint32_t pixel = (uint32_t)(g % wp.npix);
-    const uint32_t sample = (uint32_t)wp.spp_begin + (uint32_t)(g / wp.npix);
-    const Stream st{wp.seed, pixel, sample};
-    const Ray r = generate_ray(cam, st, (int)(pixel / wp.width), (int)(pixel % wp.width));
-    const uint32_t slot = n_cur + idx;
-    const bool bad = isnan(r.d.x) || isnan(r.d.y) || isnan(r.d.z); // fisheye outside the image circle: contributes exactly 0
-    store_path(cur, slot, r, v3(1.0, 1.0, 1.0), bad ? B200_DEAD : pixel, sample, 0, make_setup(wp.bound, r));
-    if (bad) atomicAdd(nan_samples, 1ull);
+  __shared__ uint32_t warp_live[8], cta_base;
+  for (uint32_t first = blockIdx.x * blockDim.x; first < n_new; first += gridDim.x * blockDim.x) {
+    const uint32_t idx = first + threadIdx.x;
+    const bool in = idx < n_new;
+    Ray r{};
+    uint32_t pixel = 0, sample = 0;
+    bool bad = false;
+    if (in) {
+      const unsigned long long g = g0 + idx;
+      pixel = (uint32_t)(g % wp.npix);
+      sample = (uint32_t)wp.spp_begin + (uint32_t)(g / wp.npix);
+      r = generate_ray(cam, Stream{wp.seed, pixel, sample}, (int)(pixel / wp.width), (int)(pixel % wp.width));
+      bad = isnan(r.d.x) || isnan(r.d.y) || isnan(r.d.z); // fisheye outside the image circle: contributes exactly 0
+    }
+    if (COMPACT) {
+      const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+      const unsigned live = __ballot_sync(0xffffffffu, in && !bad);
+      if (lane == 0) warp_live[wib] = __popc(live);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        uint32_t tot = 0;
+        for (int k = 0; k < 8; k++) tot += warp_live[k];
+        const uint32_t n_in = min(blockDim.x, n_new - first);
+        cta_base = tot ? atomicAdd(&c->n_gen, tot) : 0u;
+        if (n_in > tot) atomicAdd(&c->nan_samples, (unsigned long long)(n_in - tot));
+      }
+      __syncthreads();
+      uint32_t pos = cta_base + __popc(live & ((1u << lane) - 1u));
+      for (int k = 0; k < wib; k++) pos += warp_live[k];
+      if (in && !bad) store_path(cur, n_cur + pos, r, v3(1.0, 1.0, 1.0), pixel, sample, 0, make_setup(wp.bound, r));
+      __syncthreads(); // warp_live / cta_base are rewritten by the next iteration
+    } else if (in) {
+      store_path(cur, n_cur + idx, r, v3(1.0, 1.0, 1.0), bad ? B200_DEAD : pixel, sample, 0, make_setup(wp.bound, r));
+      if (bad) atomicAdd(&c->nan_samples, 1ull);
+    }
   }
 }
 

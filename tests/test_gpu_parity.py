@@ -193,6 +193,31 @@ def test_sample_ranges_add_up_and_wave_size_is_irrelevant(ctx):
     assert st["rays"] == st2["rays"] and st["samples"] == st2["samples"] == 24 * g.cam_small.image_width * g.cam_small.image_height
 
 
+@pytest.mark.parametrize("name", ["fox", "skybox_fisheye"])
+def test_fisheye_samples_outside_the_image_circle_are_dropped_not_lost(ctx, name):
+    """Fisheye cameras: k_generate<COMPACT> drops the samples that produce no ray (src/camera.h:268-282, NaN direction) and tops
+    the wave up in a second pass.  Small waves force many partially filled waves: every sample must still be counted exactly
+    once (samples, nan_samples, rays) and the sums must not depend on the wave size or on how the range is cut."""
+    g = golden(name)
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(g.cam_small)
+    npix = g.cam_small.image_width * g.cam_small.image_height
+    whole, st = ctx.render(99, 0, 20)
+    assert st["samples"] == 20 * npix and 0 < st["nan_samples"] < st["samples"]
+    try:
+        for wave in (1024, 5000, 1 << 16):
+            ctx.set_option(abi.OPT_WAVE_PATHS, wave)
+            img, st2 = ctx.render(99, 0, 20)
+            assert (st2["samples"], st2["nan_samples"], st2["rays"]) == (st["samples"], st["nan_samples"], st["rays"]), wave
+            assert np.allclose(np.nan_to_num(whole), np.nan_to_num(img), rtol=1e-12, atol=1e-12), wave
+        a, sa = ctx.render(99, 0, 7)
+        b, sb = ctx.render(99, 7, 20)
+        assert sa["nan_samples"] + sb["nan_samples"] == st["nan_samples"] and sa["rays"] + sb["rays"] == st["rays"]
+        assert np.allclose(np.nan_to_num(whole), np.nan_to_num(a + b), rtol=1e-12, atol=1e-12)
+    finally:
+        ctx.set_option(abi.OPT_WAVE_PATHS, 1 << 25)
+
+
 @pytest.mark.parametrize("name", ["rtow", "rtnw", "fox", "cornell_volume", "three_ball_lens", "skybox_fisheye"])
 def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
     """Lane refill and speculative (postponed-leaf) traversal change the order in which leaves are tested, never the hit:
