@@ -69,6 +69,7 @@ struct b200rt_ctx {
   int fuse_miss = 1;
   int bvh_builder = B200RT_BVH_HOST_SAH;
   int bvh_width = 0; // 0 = by scene size, 2, 4
+  uint32_t tail_paths = 32768; // k_tail finishes the frame once every sample is generated and at most this many paths live (0 = off)
   int extend_stages = 2; // 1 is within 1 % on RTOW / RTNW / Cornell and 11 % slower on Fox (profiles/r01_h_tune_l1.txt)
   int carveout_pct = -1; // -1 = computed from the kernel's footprint
   // scene
@@ -338,6 +339,10 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
   case B200RT_OPT_BVH_BUILDER:
     if (value != B200RT_BVH_HOST_SAH && value != B200RT_BVH_DEVICE_LBVH) return fail(B200RT_ERR_INVALID, "BVH builder must be 0 (host SAH) or 1 (device LBVH)");
     c->bvh_builder = (int)value; // takes effect at the next b200rt_upload_scene
+    return B200RT_OK;
+  case B200RT_OPT_TAIL_PATHS:
+    if (!(value >= 0 && value <= 1048576.0)) return fail(B200RT_ERR_INVALID, "tail paths must be in [0, 2^20]");
+    c->tail_paths = (uint32_t)value;
     return B200RT_OK;
   case B200RT_OPT_EXTEND_STAGES:
     if (value != 1 && value != 2) return fail(B200RT_ERR_INVALID, "extend stages must be 1 or 2");
@@ -667,6 +672,8 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
     k_generate<false><<<g_gen, 256, 0, s>>>(w.ctl, cur, cam, wp);
     k_ctl_generated<<<1, 1, 0, s>>>(w.ctl, 0);
   }
+  const bool tail = !mirror && c->tail_paths > 0;
+  if (tail) k_tail<<<(int)((c->tail_paths + 63) / 64), 64, 0, s>>>(w.ctl, c->S, cur, d_rgb_sum, wp, c->tail_paths);
   if (ext_events) {
     cudaEvent_t a, b;
     CU(cudaEventCreate(&a));
@@ -701,7 +708,7 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
   if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(w.ctl, w.hits, w.queues);
   const int n_shade = mirror ? launch_shades<true>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp) : launch_shades<false>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp);
   k_ctl_swap<<<1, 1, 0, s>>>(w.ctl);
-  return (mirror ? 2 : 3) + n_gen_launches + n_shade;
+  return (mirror ? 2 : 3) + (tail ? 1 : 0) + n_gen_launches + n_shade;
 }
 
 } // namespace

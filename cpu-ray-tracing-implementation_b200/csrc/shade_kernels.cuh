@@ -103,6 +103,61 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
   }
 }
 
+// ------------------------------------------------------------------------------------------------ tail
+// The last paths of a frame: once every sample has been generated and at most `limit` paths are alive, each remaining path
+// is followed to its end by one thread (trace -> shade -> trace ...) instead of ten launches per nearly empty wave (with
+// max_depth 50 most waves of a frame carry a fraction of a percent of the paths).  Same functions, same Philox draws
+// (keyed by pixel, sample, bounce), so the contribution of every path is unchanged.  The last CTA to finish empties the
+// wave (n_cur = 0): the kernels that follow in the stream find nothing to do.  c->fetch serves as the finished-CTA counter
+// (k_ctl_generated has just zeroed it, k_extend_persistent will see n_cur == 0 and not use it).
+__global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, PathBuf cur, double *accum, WaveParams wp, uint32_t limit) {
+  const uint32_t n = c->n_cur;
+  if (n == 0 || n > limit || c->next_sample != c->total_samples) return;
+  unsigned long long my_rays = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    V T;
+    const PathHead ph = load_head(cur, i, &T);
+    if (ph.pixel == B200_DEAD) continue;
+    Ray r = ph.r;
+    const Stream st{wp.seed, ph.pixel, ph.sample};
+    int bounce = (int)ph.bounce;
+    for (;;) {
+      const Best b = trace_closest(S, r, 0.001, B200_INF, st, bounce);
+      my_rays++;
+      if (b.entry < 0) {
+        accumulate(accum, ph.pixel, T * miss_color(S, r));
+        break;
+      }
+      const Entry e = S.entries[b.entry];
+      Rec rec;
+      finish_hit(S, e, r, b.t, rec, B200_UV_IF_USED);
+      Scatter sc;
+      switch (S.materials[entry_material(S, e)].kind) {
+      case B200RT_MAT_DIFFUSE_LIGHT: sc = shade_hit<B200RT_MAT_DIFFUSE_LIGHT>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_LAMBERTIAN: sc = shade_hit<B200RT_MAT_LAMBERTIAN>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_METAL: sc = shade_hit<B200RT_MAT_METAL>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_DIELECTRIC: sc = shade_hit<B200RT_MAT_DIELECTRIC>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_GLOSS: sc = shade_hit<B200RT_MAT_GLOSS>(S, rec, r, st, bounce); break;
+      default: sc = shade_hit<B200RT_MAT_ISOTROPIC>(S, rec, r, st, bounce); break;
+      }
+      if (sc.ends) {
+        accumulate(accum, ph.pixel, T * sc.value);
+        break;
+      }
+      T = T * sc.value;
+      bounce += 1;
+      if (!(bounce < wp.max_depth) || (wp.kill_zero && T.x == 0.0 && T.y == 0.0 && T.z == 0.0)) break;
+      r = Ray{rec.p, sc.dir, r.tm};
+    }
+  }
+  if (my_rays) atomicAdd(&c->rays, my_rays);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&c->fetch, 1u) == gridDim.x - 1) c->n_cur = 0;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ batch entry points
 template <bool MIRROR>
 __global__ void __launch_bounds__(128) k_trace(DevScene S, const double *rays7, size_t n, double lo, double hi, uint64_t seed, int32_t *prim,

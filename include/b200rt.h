@@ -229,6 +229,8 @@ typedef enum b200rt_option {
   B200RT_OPT_BVH_WIDTH = 12,    /* children per node of the traversed tree: 2, 4 (collapsed from the host SAH BVH2), 0 (default) = 4 above 2048 primitives */
   B200RT_OPT_PIPELINES = 13,    /* 1 or 2 (default): with 2 the sample range is split into two independent wavefronts on two streams; each half's kernels fill the SMs the other half's kernel has drained */
   B200RT_OPT_PIPE_EXTEND_CTAS = 14, /* tuning: resident extend CTAs per SM in two-pipeline mode (1..4, default 4; fewer leave registers for the other half's kernels and were measured slower) */
+  B200RT_OPT_TAIL_PATHS = 15, /* tuning: once every sample is generated and at most this many paths are alive, one kernel follows each of them to its
+                                 end instead of one wave per bounce (default 32768; 0 = off).  Same draws, same contributions */
   B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 8 from 32 Ki BVH nodes) */
 } b200rt_option;
 

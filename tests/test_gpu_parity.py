@@ -193,6 +193,28 @@ def test_sample_ranges_add_up_and_wave_size_is_irrelevant(ctx):
     assert st["rays"] == st2["rays"] and st["samples"] == st2["samples"] == 24 * g.cam_small.image_width * g.cam_small.image_height
 
 
+@pytest.mark.parametrize("name", ["cornell", "rtow", "rtnw", "fox", "cornell_volume", "cornell_specular", "three_ball_lens", "light_earth"])
+def test_tail_kernel_does_not_change_the_image(ctx, name):
+    """B200RT_OPT_TAIL_PATHS: finishing the last paths of a frame in one kernel (k_tail) instead of one wave per bounce uses the
+    same functions and the same draws: sums equal up to fp64 atomic order, rays and samples counted exactly the same.  2^20
+    sends the whole small frame through k_tail as soon as its samples are generated; 0 switches it off."""
+    g = golden(name)
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(g.cam_small)
+    try:
+        ctx.set_option(abi.OPT_TAIL_PATHS, 0)
+        base, st = ctx.render(2024, 0, 12)
+        for tail in (1 << 20, 32768, 600):
+            ctx.set_option(abi.OPT_TAIL_PATHS, tail)
+            img, st2 = ctx.render(2024, 0, 12)
+            assert (st2["samples"], st2["nan_samples"], st2["rays"]) == (st["samples"], st["nan_samples"], st["rays"]), tail
+            assert np.allclose(np.nan_to_num(base), np.nan_to_num(img), rtol=1e-12, atol=1e-12), tail
+            if tail == 1 << 20:
+                assert st2["waves"] < st["waves"]
+    finally:
+        ctx.set_option(abi.OPT_TAIL_PATHS, 32768)
+
+
 @pytest.mark.parametrize("name", ["fox", "skybox_fisheye"])
 def test_fisheye_samples_outside_the_image_circle_are_dropped_not_lost(ctx, name):
     """Fisheye cameras: k_generate<COMPACT> drops the samples that produce no ray (src/camera.h:268-282, NaN direction) and tops
