@@ -75,12 +75,15 @@ def main():
     ap.add_argument("--builder", type=int, default=0, help="0 = host SAH BVH (default), 1 = device LBVH (csrc/bvh_gpu.cuh)")
     ap.add_argument("--width", type=int, default=0, help="BVH width: 0 = automatic, 2, 4")
     ap.add_argument("--pipelines", type=int, default=2, help="independent wavefronts on two streams (1 also reports the extend share)")
+    ap.add_argument("--tail", type=int, default=-1, help="B200RT_OPT_TAIL_PATHS (-1 = library default, 0 = off)")
     ap.add_argument("--mirror", action="store_true", help="also time the node-for-node mirror traversal (parity arbiter)")
     args = ap.parse_args()
     ctx = pkg.backend.Context(0)
     ctx.set_option(abi.OPT_BVH_BUILDER, args.builder)
     ctx.set_option(abi.OPT_BVH_WIDTH, args.width)
     ctx.set_option(abi.OPT_PIPELINES, args.pipelines)
+    if args.tail >= 0:
+        ctx.set_option(abi.OPT_TAIL_PATHS, args.tail)
     for name in args.scenes.split(","):
         t0 = time.perf_counter()
         sc, cam = load(name)
