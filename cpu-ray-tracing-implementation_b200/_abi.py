@@ -16,7 +16,7 @@ MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_GLOSS, MAT_ISOTROPIC, MAT_DIFFUSE
 TEX_SOLID, TEX_CHECKER, TEX_PICTURE, TEX_PERLIN, TEX_VALUE, TEX_WORLEY, TEX_VORONOI = 0, 1, 2, 3, 4, 5, 6
 LIGHT_NONE, LIGHT_QUAD, LIGHT_SPHERE, LIGHT_DEFAULT = 0, 1, 2, 3
 CAM_PERSPECTIVE, CAM_ORTHOGRAPHIC, CAM_FISHEYE, CAM_LENS = 0, 1, 2, 3
-OPT_TRAVERSAL, OPT_WAVE_PATHS, OPT_KILL_ZERO_WEIGHT, OPT_BVH_LEAF_SIZE, OPT_SMEM_NODES, OPT_REFILL_LANES, OPT_EXTEND_BLOCKS, OPT_SPECULATIVE_LEAF, OPT_FUSE_MISS, OPT_EXTEND_STAGES, OPT_SMEM_CARVEOUT, OPT_BVH_BUILDER, OPT_BVH_WIDTH, OPT_PIPELINES, OPT_PIPE_EXTEND_CTAS, OPT_TAIL_PATHS = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15
+OPT_TRAVERSAL, OPT_WAVE_PATHS, OPT_KILL_ZERO_WEIGHT, OPT_BVH_LEAF_SIZE, OPT_RESERVED_4, OPT_REFILL_LANES, OPT_EXTEND_BLOCKS, OPT_SPECULATIVE_LEAF, OPT_FUSE_MISS, OPT_EXTEND_STAGES, OPT_SMEM_CARVEOUT, OPT_BVH_BUILDER, OPT_BVH_WIDTH, OPT_PIPELINES, OPT_PIPE_EXTEND_CTAS, OPT_TAIL_PATHS = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15
 BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1
 TRAVERSAL_FAST, TRAVERSAL_MIRROR = 0, 1
 
@@ -162,6 +162,7 @@ EXPORTS = [
     "b200rt_format_ppm",
     "b200rt_bvh_info_get",
     "b200rt_texture_sample",
+    "b200rt_scatter",
     "b200rt_abi_sizeof",
 ]
 
@@ -186,6 +187,7 @@ def bind(lib):
     lib.b200rt_format_ppm.argtypes = [vp, vp, i32, vp, sz, C.POINTER(sz)]
     lib.b200rt_bvh_info_get.argtypes = [vp, C.POINTER(BvhInfo)]
     lib.b200rt_texture_sample.argtypes = [vp, i32, vp, sz, vp]
+    lib.b200rt_scatter.argtypes = [vp, vp, vp, vp, sz, vp]
     lib.b200rt_abi_sizeof.argtypes = [i32]
     for name in EXPORTS:
         if name not in ("b200rt_last_error", "b200rt_abi_sizeof", "b200rt_ppm_bound"):

@@ -104,6 +104,15 @@ class Context:
         self._check(self._lib.b200rt_texture_sample(self._h, tex, uvp.ctypes.data, len(uvp), rgb.ctypes.data))
         return rgb
 
+    def scatter(self, rays, rec12, draws6):
+        """One level of ray_color below the hit test on supplied hit records and supplied draws (b200rt_scatter) -> (n, 16)."""
+        rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 7)
+        rec12 = np.ascontiguousarray(rec12, dtype=np.float64).reshape(-1, 12)
+        draws6 = np.ascontiguousarray(draws6, dtype=np.float64).reshape(-1, 6)
+        out = np.zeros((len(rays), 16), np.float64)
+        self._check(self._lib.b200rt_scatter(self._h, rays.ctypes.data, rec12.ctypes.data, draws6.ctypes.data, len(rays), out.ctypes.data))
+        return out
+
     def generate_rays(self, seed, spp_begin, spp_end):
         n = (spp_end - spp_begin) * self.camera.image_width * self.camera.image_height
         rays = np.zeros((n, 7), np.float64)

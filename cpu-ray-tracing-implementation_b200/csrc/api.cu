@@ -80,6 +80,7 @@ struct b200rt_ctx {
   double scene_h2d_bytes = 0;
   int graph_depth = 0;
   int bg_mode = 0; // WaveParams::fused_miss for this scene
+  uint32_t n_materials = 0;
   uint32_t kinds_present = 0; // bit k: some material of the scene has b200rt_material_kind k (queues of absent kinds stay empty)
   // camera
   b200rt_camera cam{};
@@ -320,7 +321,6 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     if (!(value >= 0 && value <= 8)) return fail(B200RT_ERR_INVALID, "leaf size must be in [0, 8] (0 = automatic)");
     c->bvh_leaf = (int)value; // takes effect at the next b200rt_upload_scene
     return B200RT_OK;
-  case B200RT_OPT_SMEM_NODES: return B200RT_OK; // reserved
   case B200RT_OPT_EXTEND_BLOCKS: c->extend_blocks = (int)value; return B200RT_OK;
   case B200RT_OPT_SPECULATIVE_LEAF: c->speculative = value != 0; return B200RT_OK;
   case B200RT_OPT_FUSE_MISS: c->fuse_miss = value != 0; return B200RT_OK;
@@ -396,6 +396,9 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
       bvh = BvhBuilder(fs.boxes, c->bvh_leaf ? c->bvh_leaf : (fs.boxes.size() <= 8192 ? 1 : 2)).run();
       ordered.resize(fs.entries.size());
       for (size_t k = 0; k < ordered.size(); k++) ordered[k] = fs.entries[bvh.perm[k]];
+      // node_step pushes at most one reference per level: a tree deeper than the traversal stack would drop subtrees silently
+      if (bvh.max_depth > B200_STACK)
+        return fail(B200RT_ERR_UNSUPPORTED, "host BVH build: depth %u exceeds the traversal stack (%d)", bvh.max_depth, B200_STACK);
     }
   } catch (const std::exception &e) {
     return fail(B200RT_ERR_INVALID, "scene description: %s", e.what());
@@ -465,6 +468,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
     c->bvh_info.sah_cost = bvh.sah_cost;
   }
   c->graph_depth = fs.graph_depth;
+  c->n_materials = d->n_materials;
   c->kinds_present = 0;
   for (uint32_t i = 0; i < d->n_materials; i++) c->kinds_present |= 1u << d->materials[i].kind;
   c->bg_mode = d->background_tex < 0 ? 1 : 0;
@@ -584,6 +588,32 @@ int b200rt_texture_sample(b200rt_ctx *c, int tex, const double *uvp5, size_t n, 
   return B200RT_OK;
 }
 
+int b200rt_scatter(b200rt_ctx *c, const double *rays7, const double *rec12, const double *draws6, size_t n, double *out16) {
+  if (!c) return fail(B200RT_ERR_INVALID, "context is NULL");
+  if (!c->have_scene) return fail(B200RT_ERR_STATE, "b200rt_scatter before b200rt_upload_scene");
+  if (n == 0) return B200RT_OK;
+  if (!rays7 || !rec12 || !draws6 || !out16) return fail(B200RT_ERR_INVALID, "NULL buffer");
+  for (size_t i = 0; i < n; i++) {
+    const double m = rec12[12 * i + 10];
+    if (!(m >= 0 && m < (double)c->n_materials) || m != (double)(int)m) return fail(B200RT_ERR_INVALID, "b200rt_scatter: record %zu names material %g (scene has %u)", i, m, c->n_materials);
+  }
+  CU(cudaSetDevice(c->device));
+  DevMem tmp;
+  double *d_r = nullptr, *d_h = nullptr, *d_u = nullptr, *d_o = nullptr;
+  CU(tmp.alloc((void **)&d_r, n * 7 * sizeof(double)));
+  CU(tmp.alloc((void **)&d_h, n * 12 * sizeof(double)));
+  CU(tmp.alloc((void **)&d_u, n * 6 * sizeof(double)));
+  CU(tmp.alloc((void **)&d_o, n * 16 * sizeof(double)));
+  CU(cudaMemcpyAsync(d_r, rays7, n * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_h, rec12, n * 12 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_u, draws6, n * 6 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  k_scatter<<<grid_for(c, n, 128, 16), 128, 0, c->stream>>>(c->S, d_r, d_h, d_u, n, d_o);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(out16, d_o, n * 16 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return B200RT_OK;
+}
+
 int b200rt_generate_rays(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_end, double *rays7) {
   if (!c || !rays7) return fail(B200RT_ERR_INVALID, "NULL argument");
   if (!c->have_camera) return fail(B200RT_ERR_STATE, "b200rt_generate_rays before b200rt_set_camera");
@@ -675,10 +705,10 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
   const bool tail = !mirror && c->tail_paths > 0;
   if (tail) k_tail<<<(int)((c->tail_paths + 63) / 64), 64, 0, s>>>(w.ctl, c->S, cur, d_rgb_sum, wp, c->tail_paths);
   if (ext_events) {
-    cudaEvent_t a, b;
+    cudaEvent_t a, b; // owned by the caller's guard from the moment they exist
     CU(cudaEventCreate(&a));
-    CU(cudaEventCreate(&b));
     ext_events->push_back(a);
+    CU(cudaEventCreate(&b));
     ext_events->push_back(b);
     CU(cudaEventRecord(a, s));
   }
@@ -726,6 +756,10 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   const unsigned long long total = (unsigned long long)npix * (unsigned long long)(spp_end - spp_begin);
   if (stats) std::memset(stats, 0, sizeof *stats);
   if (total == 0) return B200RT_OK;
+  if (c->cam.max_depth <= 0) { // ray_color(iteration <= 0) returns color(0) before it traces anything (src/camera.h:194-195): every sample adds 0
+    if (stats) stats->samples = total;
+    return B200RT_OK;
+  }
   const bool mirror = c->traversal == B200RT_TRAVERSAL_MIRROR;
   // Two pipelines: the sample range is split in two halves that run as independent wavefronts on two streams, so that one
   // half's kernels fill the SMs that the other half's kernel has already drained (every launch ends with a tail of
@@ -771,7 +805,33 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     }
   }
 
-  std::vector<cudaEvent_t> ext_events;
+  // Whatever happens below (a failed launch, a failed copy), the forked pipeline streams are joined back into the caller's
+  // stream and the per-launch timing events are destroyed: the caller may keep using `s` and d_rgb_sum after an error.
+  struct WaveLoopGuard {
+    b200rt_ctx *c;
+    cudaStream_t s;
+    cudaStream_t *ps;
+    int n_pipe;
+    std::vector<cudaEvent_t> ext_events;
+    bool joined = false;
+    cudaError_t join() {
+      if (joined) return cudaSuccess;
+      joined = true;
+      cudaError_t first = cudaSuccess;
+      if (n_pipe > 1)
+        for (int p = 0; p < n_pipe; p++) {
+          cudaError_t e = cudaEventRecord(c->w[p].done, ps[p]);
+          if (e == cudaSuccess) e = cudaStreamWaitEvent(s, c->w[p].done, 0);
+          if (e != cudaSuccess && first == cudaSuccess) first = e;
+        }
+      return first;
+    }
+    ~WaveLoopGuard() {
+      join();
+      for (cudaEvent_t e : ext_events) cudaEventDestroy(e);
+    }
+  } guard{c, s, ps, n_pipe};
+  std::vector<cudaEvent_t> &ext_events = guard.ext_events;
   if (stats) CU(cudaEventRecord(c->ev0, s));
   unsigned long long launches = 0, wave = 0, next_check = 0;
   bool done[B200_MAX_PIPELINES];
@@ -789,6 +849,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
       if (n < 0) return n;
       launches += (unsigned long long)n;
     }
+    CU(cudaGetLastError()); // launch-configuration errors surface here, once per wave
     wave++;
     if (wave >= next_check) {
       for (int p = 0; p < n_pipe; p++)
@@ -809,12 +870,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
       next_check = wave + ahead;
     }
   }
-  CU(cudaGetLastError());
-  if (n_pipe > 1) // the caller's stream continues when every part is in the accumulator
-    for (int p = 0; p < n_pipe; p++) {
-      CU(cudaEventRecord(c->w[p].done, ps[p]));
-      CU(cudaStreamWaitEvent(s, c->w[p].done, 0));
-    }
+  CU(guard.join()); // the caller's stream continues when every part is in the accumulator
   if (stats) {
     CU(cudaEventRecord(c->ev1, s));
     CU(cudaEventSynchronize(c->ev1));
@@ -827,7 +883,6 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
       cudaEventElapsedTime(&e, ext_events[k], ext_events[k + 1]);
       ext += e;
     }
-    for (cudaEvent_t e : ext_events) cudaEventDestroy(e);
     stats->extend_ms = ext; // not measured with two pipelines (the kernels of the halves overlap)
     stats->samples = total;
     for (int p = 0; p < n_pipe; p++) stats->rays += c->w[p].h_ctl->rays, stats->nan_samples += c->w[p].h_ctl->nan_samples;

@@ -108,8 +108,8 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
 // is followed to its end by one thread (trace -> shade -> trace ...) instead of ten launches per nearly empty wave (with
 // max_depth 50 most waves of a frame carry a fraction of a percent of the paths).  Same functions, same Philox draws
 // (keyed by pixel, sample, bounce), so the contribution of every path is unchanged.  The last CTA to finish empties the
-// wave (n_cur = 0): the kernels that follow in the stream find nothing to do.  c->fetch serves as the finished-CTA counter
-// (k_ctl_generated has just zeroed it, k_extend_persistent will see n_cur == 0 and not use it).
+// wave (n_cur = 0): the kernels that follow in the stream find nothing to do.  WaveCtl::tail_done counts the finished CTAs
+// (zeroed by k_ctl_init / k_ctl_generated; no other kernel touches it).
 __global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, PathBuf cur, double *accum, WaveParams wp, uint32_t limit) {
   const uint32_t n = c->n_cur;
   if (n == 0 || n > limit || c->next_sample != c->total_samples) return;
@@ -154,7 +154,7 @@ __global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, PathBuf cur, do
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
-    if (atomicAdd(&c->fetch, 1u) == gridDim.x - 1) c->n_cur = 0;
+    if (atomicAdd(&c->tail_done, 1u) == gridDim.x - 1) c->n_cur = 0;
   }
 }
 
@@ -182,6 +182,36 @@ __global__ void __launch_bounds__(128) k_trace(DevScene S, const double *rays7, 
     if (front) front[i] = ok && rec.front_face ? 1 : 0;
     if (p) p[3 * i] = ok ? rec.p.x : 0.0, p[3 * i + 1] = ok ? rec.p.y : 0.0, p[3 * i + 2] = ok ? rec.p.z : 0.0;
     if (normal) normal[3 * i] = ok ? rec.normal.x : 0.0, normal[3 * i + 1] = ok ? rec.normal.y : 0.0, normal[3 * i + 2] = ok ? rec.normal.z : 0.0;
+  }
+}
+
+// One level of ray_color below the hit test on caller-supplied hit records and caller-supplied draws (b200rt_scatter).
+// rec12 = {p[3], normal[3], t, u, v, front_face, material row, 0}; draws6 = {m0 m1 m2 s0 s1 s2};
+// out16 = {mode, emitted[3], attenuation[3], dir[3], pdf_value, p_scattered, weight[3], 0} with weight = what multiplies the
+// incoming radiance: attenuation (kDetermined) or attenuation * p_scattered / pdf_value (kRandom).
+__global__ void __launch_bounds__(128) k_scatter(DevScene S, const double *rays7, const double *rec12, const double *draws6, size_t n, double *out16) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const double *q = rays7 + 7 * i, *h = rec12 + 12 * i, *u = draws6 + 6 * i;
+    const Ray r{v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6]};
+    Rec rec;
+    rec.p = v3(h[0], h[1], h[2]), rec.normal = v3(h[3], h[4], h[5]);
+    rec.t = h[6], rec.u = h[7], rec.v = h[8];
+    rec.front_face = h[9] != 0.0;
+    rec.mat = (int)h[10];
+    rec.prim = -1;
+    FixedDraws fd;
+    fd.m = Draws{u[0], u[1], u[2], 0.0};
+    fd.s = Draws{u[3], u[4], u[5], 0.0};
+    ScatterDetail det;
+    const Scatter sc = shade_hit<-1, FixedDraws>(S, rec, r, fd, 0, &det);
+    double *o = out16 + 16 * i;
+    o[0] = (double)det.mode;
+    o[1] = det.emitted.x, o[2] = det.emitted.y, o[3] = det.emitted.z;
+    o[4] = det.attenuation.x, o[5] = det.attenuation.y, o[6] = det.attenuation.z;
+    o[7] = sc.dir.x, o[8] = sc.dir.y, o[9] = sc.dir.z;
+    o[10] = det.pdf_value, o[11] = det.p_scattered;
+    const V w = det.mode == 0 ? v3(0, 0, 0) : sc.value;
+    o[12] = w.x, o[13] = w.y, o[14] = w.z, o[15] = 0.0;
   }
 }
 

@@ -109,15 +109,33 @@ struct Scatter {
   V dir;       // direction of the scattered ray (origin = rec.p, time = incoming time)
 };
 
+// The factors ray_color combines (src/camera.h:202-240), kept apart for the parity entry b200rt_scatter.
+struct ScatterDetail {
+  int mode;       // 0 = scatter() returned false (emission only), 1 = kDetermined, 2 = kRandom
+  V emitted;      // material::emitted
+  V attenuation;  // scatter_record.attenuation
+  double pdf_value, p_scattered;
+};
+// Draws handed in by the caller instead of Philox (b200rt_scatter): m = what material::scatter consumes, s = what the pdf does.
+struct FixedDraws {
+  Draws m, s;
+  DEV Draws get(int, int purpose, uint32_t) const { return purpose == P_MATERIAL ? m : s; }
+};
+
 // One level of ray_color below the hit test (src/camera.h:202-240).  `b` = scatters so far on this path.
 // KIND >= 0: the caller knows the material kind at compile time (material-sorted queues), so only that branch is compiled in.
-template <int KIND = -1> DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const Stream &st, int b) {
+// STREAM: where the draws come from (Stream = Philox by path address).  det: optional breakdown (constant nullptr on the hot path).
+template <int KIND = -1, class STREAM = Stream>
+DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const STREAM &st, int b, ScatterDetail *det = nullptr) {
   Scatter out;
+  if (det) det->mode = 0, det->emitted = v3(0, 0, 0), det->attenuation = v3(0, 0, 0), det->pdf_value = 0, det->p_scattered = 0;
   b200rt_material m = S.materials[rec.mat];
   if (KIND >= 0) m.kind = KIND;
   if (m.kind == B200RT_MAT_DIFFUSE_LIGHT) { // src/material.h:211-215; scatter() is the base's false (:43)
     out.ends = true;
     out.value = rec.front_face ? tex_sample(S, m.tex, rec.u, rec.v, rec.p) : v3(0, 0, 0);
+    out.dir = v3(0, 0, 0);
+    if (det) det->emitted = out.value;
     return out;
   }
   out.ends = false;
@@ -175,8 +193,10 @@ template <int KIND = -1> DEV Scatter shade_hit(const DevScene &S, const Rec &rec
     pdf_kind = 2;
     break;
   }
+  if (det) det->attenuation = attenuation;
   if (determined) { // src/camera.h:210-214
     out.value = attenuation;
+    if (det) det->mode = 1;
     return out;
   }
   // kRandom, src/camera.h:217-240
@@ -202,6 +222,7 @@ template <int KIND = -1> DEV Scatter shade_hit(const DevScene &S, const Rec &rec
   }
   out.dir = dir;
   out.value = (attenuation * p_scattered) / pdf_value;
+  if (det) det->mode = 2, det->pdf_value = pdf_value, det->p_scattered = p_scattered;
   return out;
 }
 

@@ -27,7 +27,7 @@ struct WaveCtl {
   unsigned long long next_sample, total_samples, rays, nan_samples, waves, extend_rays_dummy;
   uint32_t n_cur, n_next, capacity, fetch; // fetch: next unclaimed 32-ray batch of the persistent extend kernel
   uint32_t q_count[8];
-  uint32_t n_gen, pad; // n_gen: live paths appended by k_generate<COMPACT> in this wave
+  uint32_t n_gen, tail_done; // n_gen: live paths appended by k_generate<COMPACT> in this wave; tail_done: CTAs of k_tail that have finished
 };
 
 // Path state = eight 16-byte "quads" per path.  The fp32 box-filter constants (traverse.cuh) are computed by the PRODUCER
@@ -147,6 +147,7 @@ __global__ void k_ctl_init(WaveCtl *c, unsigned long long total, uint32_t capaci
   c->capacity = capacity;
   c->fetch = 0;
   c->n_gen = 0;
+  c->tail_done = 0;
   for (int k = 0; k < 8; k++) c->q_count[k] = 0;
 }
 DEV uint32_t wave_refill(const WaveCtl *c) {
@@ -159,6 +160,7 @@ __global__ void k_ctl_generated(WaveCtl *c, int compact) {
   c->next_sample += n;
   c->fetch = 0;
   c->n_gen = 0;
+  c->tail_done = 0;
 }
 __global__ void k_ctl_swap(WaveCtl *c) {
   unsigned long long r = 0;

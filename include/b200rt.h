@@ -219,7 +219,7 @@ typedef enum b200rt_option {
   B200RT_OPT_WAVE_PATHS = 1,    /* paths resident per wave, shared by the pipelines (default 32 Mi = 10 GB of wavefront state) */
   B200RT_OPT_KILL_ZERO_WEIGHT = 2, /* 1 (default): drop paths whose throughput is exactly 0 in all channels */
   B200RT_OPT_BVH_LEAF_SIZE = 3, /* max primitives per leaf of the compacted BVH; 0 (default) = 1 up to 8192 primitives, else 2 */
-  B200RT_OPT_SMEM_NODES = 4,    /* top-of-tree nodes staged in shared memory (reserved) */
+  /* 4 was B200RT_OPT_SMEM_NODES (never implemented; removed: b200rt_set_option rejects it) */
   B200RT_OPT_EXTEND_BLOCKS = 6, /* tuning: resident CTAs per SM the persistent extend kernel is compiled for (4 or 6; 6 spills and is slower: profiles/r01_g_tune.txt) */
   B200RT_OPT_SPECULATIVE_LEAF = 7, /* tuning: 1 = a lane postpones its first leaf and keeps walking inner nodes (speculative traversal) */
   B200RT_OPT_FUSE_MISS = 8,     /* 1 (default): in a scene without background the extend kernel finishes a miss itself (it adds 0) instead of queueing the path */
@@ -308,6 +308,26 @@ int b200rt_format_ppm(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, cha
 /* Replaces: texture::sample(u, v, p) (src/texture.h:9) of texture row `tex` on a batch.
  * uvp5 = n x {u, v, p[3]}, rgb = n x 3.  Host buffers. */
 int b200rt_texture_sample(b200rt_ctx *ctx, int tex, const double *uvp5, size_t n, double *rgb);
+
+/* Replaces: one level of camera::ray_color below the hit test (src/camera.h:202-240) on a batch of hit records:
+ * material::emitted and material::scatter (src/material.h:57-219), then for scatter_mode::kRandom the pdf the reference
+ * builds (scatter_record.pdf alone, or dual_pdf(hittable_pdf(light), scatter_record.pdf), src/camera.h:217-231;
+ * src/pdf.h:15-61; src/hittable_list.h:39-50; src/quad.h:66-78; src/sphere.h:76-81), its generate() and value(), and
+ * material::p_scattered.  Parity entry: the random numbers are SUPPLIED, so that the result can be compared bit for bit with
+ * the reference run on the same std::rand values.  Host buffers.
+ *   rays7  : n x {origin[3], direction[3], time}                     the incoming ray r_in
+ *   rec12  : n x {p[3], normal[3], t, u, v, front_face, material row, 0}   the hit_record (src/hittable.h:7-30)
+ *   draws6 : n x {m0, m1, m2, s0, s1, s2} in [0,1):
+ *              m* = what scatter() consumes   metal: (m1, m2) = (u1, u2) of random_in_unit_sphere (src/utility.h:30-42)
+ *                                             dielectric: m0 = the reflectance test (src/material.h:123)
+ *                                             gloss: m0 = the specular test (:161), (m1, m2) = (r1, r2) of random_cosine_direction
+ *              s* = what the pdf consumes     s0 = dual_pdf::generate's choice (src/pdf.h:53; unused without a light),
+ *                                             (s1, s2) = (r1, r2) of random_cosine_direction, (u1, u2) of random_in_unit_sphere,
+ *                                             or the factors of u_ and v_ in quad::random (src/quad.h:76)
+ *   out16  : n x {mode, emitted[3], attenuation[3], direction[3], pdf_value, p_scattered, weight[3], 0}
+ *              mode 0 = scatter() returned false, 1 = kDetermined, 2 = kRandom; direction = of the scattered ray;
+ *              weight = the factor on the incoming radiance: attenuation, or attenuation * p_scattered / pdf_value */
+int b200rt_scatter(b200rt_ctx *ctx, const double *rays7, const double *rec12, const double *draws6, size_t n, double *out16);
 
 /* sizeof() of the ABI structures as compiled into the library (0 scene_desc, 1 camera, 2 stats, 3 node, 4 material,
  * 5 texture, 6 image, 7 volume, 8 value_noise, 9 bvh_info): lets foreign-language bindings check their mirrors. */

@@ -505,44 +505,40 @@ V miss(const Scene &s, const Ray &r) {
   return v3(0, 0, 0);
 }
 
-// ------------------------------------------------------------------ camera::ray_color (src/camera.h:193-241)
-V ray_color(Ctx &cx, const Ray &r, int iteration) {
-  if (iteration <= 0) return v3(0, 0, 0);
-  const Scene &s = cx.sc;
-  Rec rec;
-  const V &d = r.d;
-  if (!(std::isnan(d.x) || std::isnan(d.y) || std::isnan(d.z))) cx.rays++; // counting rule of SURVEY.md §8d
-  if (!node_hit(cx, (int)s.d->root, r, Interval{0.001, infinity}, rec, 0)) return miss(s, r);
-
+// ------------------------------------------------------------------ one level of ray_color below the hit test
+// (src/camera.h:202-240): material::emitted, material::scatter, the pdf the reference builds, generate / value, p_scattered.
+// dm = the draws scatter() consumes, ds = the draws the pdf consumes (addressing documented at b200rt_scatter, include/b200rt.h).
+struct Shade {
+  int mode;      // 0 = scatter() returned false, 1 = kDetermined, 2 = kRandom
+  V emitted;     // color_from_emission (:205)
+  V attenuation; // scatter_record.attenuation
+  V dir;         // direction of the scattered ray
+  double pdf_value, p_scattered;
+};
+Shade shade_step(const Scene &s, const Rec &rec, const Ray &r, const Draws &dm, const Draws &ds) {
+  Shade o{0, v3(0, 0, 0), v3(0, 0, 0), v3(0, 0, 0), 0.0, 0.0};
   const b200rt_material &m = s.d->materials[rec.mat];
-  V emission = v3(0, 0, 0);
   if (m.kind == B200RT_MAT_DIFFUSE_LIGHT) { // src/material.h:211-215; scatter() is the base's `false` (:43)
-    if (rec.front_face) emission = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
-    return emission;
+    if (rec.front_face) o.emitted = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
+    return o;
   }
-
-  const int b = cx.bounce;
-  Draws dm = cx.st.get(b, P_MATERIAL, 0);
-  bool determined = false;
-  V attenuation = v3(0, 0, 0);
-  Ray scattered{rec.p, v3(0, 0, 0), r.tm};
   int pdf_kind = 0; // 1 cosine, 2 sphere
   switch (m.kind) {
   case B200RT_MAT_LAMBERTIAN: // src/material.h:62-67
-    attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
+    o.attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
     pdf_kind = 1;
     break;
   case B200RT_MAT_METAL: { // src/material.h:85-92
     V dir = unit_vector(reflect(r.d, rec.normal));
     dir = dir + (double)m.p0 * unit_vector(random_in_unit_sphere(dm.u[1], dm.u[2]));
-    determined = true;
-    scattered.d = dir;
-    attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
+    o.mode = 1;
+    o.dir = dir;
+    o.attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
     break;
   }
   case B200RT_MAT_DIELECTRIC: { // src/material.h:113-131
-    determined = true;
-    attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
+    o.mode = 1;
+    o.attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
     double ri = rec.front_face ? (1.0 / m.p0) : m.p0;
     V ud = unit_vector(r.d);
     double cos_theta = std::fmin(dot(-ud, rec.normal), 1.0);
@@ -554,9 +550,9 @@ V ray_color(Ctx &cx, const Ray &r, int iteration) {
       return r0 + (1 - r0) * std::pow((1 - cosine), 5);
     };
     if (cant_refract || reflectance(cos_theta, ri) > dm.u[0])
-      scattered.d = reflect(ud, rec.normal);
+      o.dir = reflect(ud, rec.normal);
     else
-      scattered.d = refract(ud, rec.normal, ri);
+      o.dir = refract(ud, rec.normal, ri);
     break;
   }
   case B200RT_MAT_GLOSS: { // src/material.h:158-174
@@ -565,56 +561,64 @@ V ray_color(Ctx &cx, const Ray &r, int iteration) {
     if (is_specular) {
       V diffuse_dir = Onb(rec.normal).transform(random_cosine_direction(dm.u[1], dm.u[2]));
       double t = (double)m.p0;
-      V dir = unit_vector((1 - t) * diffuse_dir + t * specular_dir); // linear_interpolation, src/utility.h:85
-      determined = true;
-      attenuation = v3(1.0, 1.0, 1.0);
-      scattered.d = dir;
+      o.dir = unit_vector((1 - t) * diffuse_dir + t * specular_dir); // linear_interpolation, src/utility.h:85
+      o.mode = 1;
+      o.attenuation = v3(1.0, 1.0, 1.0);
     } else {
-      attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
+      o.attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
       pdf_kind = 1;
     }
     break;
   }
   case B200RT_MAT_ISOTROPIC: // src/material.h:193-198
-    attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
+    o.attenuation = tex_sample(s, m.tex, rec.u, rec.v, rec.p);
     pdf_kind = 2;
     break;
   }
-
-  cx.bounce = b + 1;
-  if (determined) { // src/camera.h:210-214
-    V in = ray_color(cx, scattered, iteration - 1);
-    return attenuation * in + emission;
-  }
+  if (o.mode == 1) return o; // kDetermined, src/camera.h:210-214
 
   // kRandom: src/camera.h:217-240
-  Draws ds = cx.st.get(b, P_SAMPLE, 0);
+  o.mode = 2;
   Onb uvw(pdf_kind == 1 ? rec.normal : v3(0, 1, 0));
   auto mat_generate = [&]() -> V {
     if (pdf_kind == 1) return uvw.transform(random_cosine_direction(ds.u[1], ds.u[2])); // src/pdf.h:41
     return unit_vector(random_in_unit_sphere(ds.u[1], ds.u[2]));                        // src/pdf.h:19
   };
   auto mat_value = [&](V dir) -> double { return pdf_kind == 1 ? cosine_pdf_value(uvw, dir) : 1 / (4 * pi); };
-  V dir;
-  double pdf_value;
   if (s.d->light_kind == B200RT_LIGHT_NONE) {
-    dir = mat_generate();
-    pdf_value = mat_value(dir);
+    o.dir = mat_generate();
+    o.pdf_value = mat_value(o.dir);
   } else { // dual_pdf, src/pdf.h:48-61
-    dir = (ds.u[0] < 0.5) ? light_random(s, rec.p, ds.u[1], ds.u[2]) : mat_generate();
-    pdf_value = 0.5 * light_pdf_value(s, rec.p, dir) + 0.5 * mat_value(dir);
+    o.dir = (ds.u[0] < 0.5) ? light_random(s, rec.p, ds.u[1], ds.u[2]) : mat_generate();
+    o.pdf_value = 0.5 * light_pdf_value(s, rec.p, o.dir) + 0.5 * mat_value(o.dir);
   }
-  scattered.d = dir;
-  double p_scattered;
   if (pdf_kind == 1) { // lambertian / gloss p_scattered, src/material.h:69-72,176-179
-    double cosine = dot(rec.normal, unit_vector(dir));
-    p_scattered = cosine < 0 ? 0 : cosine / pi;
+    double cosine = dot(rec.normal, unit_vector(o.dir));
+    o.p_scattered = cosine < 0 ? 0 : cosine / pi;
   } else {
-    p_scattered = 1 / (4 * pi); // src/material.h:200
+    o.p_scattered = 1 / (4 * pi); // src/material.h:200
   }
+  return o;
+}
+
+// ------------------------------------------------------------------ camera::ray_color (src/camera.h:193-241)
+V ray_color(Ctx &cx, const Ray &r, int iteration) {
+  if (iteration <= 0) return v3(0, 0, 0);
+  const Scene &s = cx.sc;
+  Rec rec;
+  const V &d = r.d;
+  if (!(std::isnan(d.x) || std::isnan(d.y) || std::isnan(d.z))) cx.rays++; // counting rule of SURVEY.md §8d
+  if (!node_hit(cx, (int)s.d->root, r, Interval{0.001, infinity}, rec, 0)) return miss(s, r);
+
+  const int b = cx.bounce;
+  const Shade sh = shade_step(s, rec, r, cx.st.get(b, P_MATERIAL, 0), cx.st.get(b, P_SAMPLE, 0));
+  if (sh.mode == 0) return sh.emitted; // :207-208
+  cx.bounce = b + 1;
+  const Ray scattered{rec.p, sh.dir, r.tm};
   V in = ray_color(cx, scattered, iteration - 1);
-  V from_scatter = (attenuation * p_scattered * in) / pdf_value;
-  return from_scatter + emission;
+  if (sh.mode == 1) return sh.attenuation * in + sh.emitted; // :210-214
+  V from_scatter = (sh.attenuation * sh.p_scattered * in) / sh.pdf_value; // :224, :237
+  return from_scatter + sh.emitted;
 }
 
 // ------------------------------------------------------------------ camera::generate_ray (src/camera.h:244-284)
@@ -684,7 +688,11 @@ struct oracle_stats {
 
 int oracle_trace(const b200rt_scene_desc *d, const double *rays7, size_t n, double tmin, double tmax, uint64_t seed, int32_t *prim, double *t,
                  double *uv, uint8_t *front, double *p, double *normal) {
-  for (size_t i = 0; i < n; i++) {
+  // rays are independent (the volume draw of ray i is keyed by i): large batches are spread over the host threads
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  const size_t n_thr = n >= 65536 ? hw : 1;
+  auto work = [&](size_t lo, size_t hi) {
+  for (size_t i = lo; i < hi; i++) {
     const double *q = rays7 + 7 * i;
     Ray r{v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6]};
     Ctx cx{Scene{d}, Stream{seed, (uint32_t)i, (uint32_t)(i >> 32)}, 0, 0};
@@ -700,6 +708,14 @@ int oracle_trace(const b200rt_scene_desc *d, const double *rays7, size_t n, doub
       if (p) p[3 * i + c] = ok ? pp[c] : 0.0;
       if (normal) normal[3 * i + c] = ok ? nn[c] : 0.0;
     }
+  }
+  };
+  if (n_thr == 1) {
+    work(0, n);
+  } else {
+    std::vector<std::thread> pool;
+    for (size_t k = 0; k < n_thr; k++) pool.emplace_back(work, n * k / n_thr, n * (k + 1) / n_thr);
+    for (auto &th : pool) th.join();
   }
   return 0;
 }
@@ -750,6 +766,31 @@ int oracle_texture_sample(const b200rt_scene_desc *d, int tex, const double *uvp
 }
 
 // ray_color on caller-supplied rays; ray i consumes the draws of stream (pixel = i, sample = 0).
+// b200rt_scatter's counterpart: same buffers (include/b200rt.h).
+int oracle_scatter(const b200rt_scene_desc *d, const double *rays7, const double *rec12, const double *draws6, size_t n, double *out16) {
+  Scene s{d};
+  for (size_t i = 0; i < n; i++) {
+    const double *q = rays7 + 7 * i, *h = rec12 + 12 * i, *u = draws6 + 6 * i;
+    Ray r{v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6]};
+    Rec rec{};
+    rec.p = v3(h[0], h[1], h[2]), rec.normal = v3(h[3], h[4], h[5]);
+    rec.t = h[6], rec.u = h[7], rec.v = h[8];
+    rec.front_face = h[9] != 0.0;
+    rec.mat = (int)h[10];
+    if (rec.mat < 0 || (uint32_t)rec.mat >= d->n_materials) return -1;
+    const Shade sh = shade_step(s, rec, r, Draws{{u[0], u[1], u[2], 0.0}}, Draws{{u[3], u[4], u[5], 0.0}});
+    double *o = out16 + 16 * i;
+    o[0] = sh.mode;
+    o[1] = sh.emitted.x, o[2] = sh.emitted.y, o[3] = sh.emitted.z;
+    o[4] = sh.attenuation.x, o[5] = sh.attenuation.y, o[6] = sh.attenuation.z;
+    o[7] = sh.dir.x, o[8] = sh.dir.y, o[9] = sh.dir.z;
+    o[10] = sh.pdf_value, o[11] = sh.p_scattered;
+    V w = sh.mode == 0 ? v3(0, 0, 0) : (sh.mode == 1 ? sh.attenuation : (sh.attenuation * sh.p_scattered) / sh.pdf_value);
+    o[12] = w.x, o[13] = w.y, o[14] = w.z, o[15] = 0.0;
+  }
+  return 0;
+}
+
 int oracle_ray_color(const b200rt_scene_desc *d, const double *rays7, size_t n, int depth, uint64_t seed, double *rgb) {
   for (size_t i = 0; i < n; i++) {
     const double *q = rays7 + 7 * i;

@@ -38,6 +38,7 @@ def lib():
         L.oracle_generate_rays.argtypes = [CAM, u64, i32, i32, vp]
         L.oracle_generate_rays_from_draws.argtypes = [CAM, sz, vp, i32, i32, vp]
         L.oracle_texture_sample.argtypes = [SD, i32, vp, sz, vp]
+        L.oracle_scatter.argtypes = [SD, vp, vp, vp, sz, vp]
         L.oracle_ray_color.argtypes = [SD, vp, sz, i32, u64, vp]
         L.oracle_render.argtypes = [SD, CAM, u64, i32, i32, i32, vp, vp, vp, C.POINTER(OracleStats)]
         _lib = L
@@ -82,6 +83,16 @@ def texture_sample(scene, tex, uvp):
     rgb = np.zeros((len(uvp), 3), np.float64)
     assert lib().oracle_texture_sample(C.byref(d), tex, uvp.ctypes.data, len(uvp), rgb.ctypes.data) == 0
     return rgb
+
+
+def scatter(scene, rays, rec12, draws6):
+    d, keep = scene.desc()
+    rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 7)
+    rec12 = np.ascontiguousarray(rec12, dtype=np.float64).reshape(-1, 12)
+    draws6 = np.ascontiguousarray(draws6, dtype=np.float64).reshape(-1, 6)
+    out = np.zeros((len(rays), 16), np.float64)
+    assert lib().oracle_scatter(C.byref(d), rays.ctypes.data, rec12.ctypes.data, draws6.ctypes.data, len(rays), out.ctypes.data) == 0
+    return out
 
 
 def ray_color(scene, rays, depth, seed=1):

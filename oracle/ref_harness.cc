@@ -480,6 +480,30 @@ void build(scene &sc, const std::string &name, const build_args &a) {
     sphereflake_gen(100, point3(0, 0, 0), std::make_shared<metal>(solid(.5)), 4, world, 0.25, vec3(0, 1, 0));
     cam.initialize_perspective(pick(a.width, 400), 1.0, point3(200), vec3(0, 0, 0), 1, 90.0, pick(a.spp, 50), pick(a.depth, 5));
     cam.background_ = picture(A + "/bathroom.exr");
+  } else if (name.rfind("zoo_", 0) == 0) {
+    // Not a scene of src/main.cc: every material (src/material.h:57-219) side by side under each kind of `light` argument that
+    // camera::render accepts (src/camera.h:135): none, a quad (src/quad.h:66-78), a sphere (src/sphere.h:76-81).
+    world.push_back(S(point3(0, -1000, 0), 1000, lamt(std::make_shared<checker_texture>(color(.9, .9, .9), color(.2, .3, .1), 0.8))));
+    world.push_back(S(point3(-4, 1, 0), 1.0, lam(.4, .2, .1)));
+    world.push_back(S(point3(-2, 1, 0), 1.0, std::make_shared<metal>(color(.7, .6, .5), 0.3)));
+    world.push_back(S(point3(0, 1, 0), 1.0, std::make_shared<dielectric>(1.5)));
+    world.push_back(S(point3(2, 1, 0), 1.0, std::make_shared<gloss>(color(.8, .3, .3), 0.6, 0.5)));
+    world.push_back(std::make_shared<volumne>(S(point3(4, 1, 0), 1.0, lam(1, 1, 1)), 0.8, solid(0.2, 0.4, 0.9)));
+    world.push_back(std::make_shared<translate>(vec3(-1.5, 0, 2.2), std::make_shared<rotate_y>(box(point3(0), point3(1, 1.4, 1), lam(.73, .73, .73)), 25)));
+    world.push_back(S(point3(1.2, 0.5, 2.6), 0.5, std::make_shared<gloss>(std::make_shared<perlin_texture>(3), 0.2, 0.1)));
+    auto ql = Q(point3(-1, 4, -1), vec3(2, 0, 0), vec3(0, 0, 2), emit(8));
+    auto sl = std::make_shared<sphere>(point3(3, 3.5, -2), 0.6, emit(10));
+    world.push_back(ql);
+    world.push_back(sl);
+    if (name == "zoo_quad")
+      light = ql;
+    else if (name == "zoo_sphere")
+      light = sl;
+    else if (name != "zoo_nolight")
+      throw std::runtime_error("unknown scene " + name);
+    use_bvh = true;
+    cam.initialize_perspective(pick(a.width, 400), 16.0 / 9.0, point3(0, 3, 9), point3(0, 1, 0), 1, 40.0, pick(a.spp, 100), pick(a.depth, 10));
+    cam.background_ = solid(.10, .12, .20);
   } else if (name == "white_sphere") {
     // src/main.cc:500-510
     world.push_back(S(point3(0, 0, 0), 1, std::make_shared<metal>(solid(1.0), 0.1)));
@@ -686,23 +710,35 @@ int ref_trace(int h, const double *rays7, size_t n, double tmin, double tmax, un
   if (!s) return -1;
   g_rng_mode = 0;
   srand(seed);
-  for (size_t i = 0; i < n; i++) {
-    const double *q = rays7 + 7 * i;
-    ray r(point3(q[0], q[1], q[2]), vec3(q[3], q[4], q[5]), q[6]);
-    hit_record rec;
-    rec.t = 0;
-    rec.u = rec.v = 0; // triangle::hit and volumne::hit leave u,v unwritten (src/triangle.h:35-39); the ABI defines them as 0
-    rec.front_face = false;
-    b200::leaf_tag::last_hit_id() = -1;
-    bool ok = s->world->hit(r, interval(tmin, tmax), rec);
-    if (prim) prim[i] = ok ? b200::leaf_tag::last_hit_id() : -1;
-    if (t) t[i] = ok ? rec.t : 0.0;
-    if (uv) uv[2 * i] = ok ? rec.u : 0.0, uv[2 * i + 1] = ok ? rec.v : 0.0;
-    if (front) front[i] = ok ? (rec.front_face ? 1 : 0) : 0;
-    for (int c = 0; c < 3; c++) {
-      if (p) p[3 * i + c] = ok ? rec.p.e[c] : 0.0;
-      if (normal) normal[3 * i + c] = ok ? rec.normal.e[c] : 0.0;
+  auto work = [&](size_t lo, size_t hi) {
+    for (size_t i = lo; i < hi; i++) {
+      const double *q = rays7 + 7 * i;
+      ray r(point3(q[0], q[1], q[2]), vec3(q[3], q[4], q[5]), q[6]);
+      hit_record rec;
+      rec.t = 0;
+      rec.u = rec.v = 0; // triangle::hit and volumne::hit leave u,v unwritten (src/triangle.h:35-39); the ABI defines them as 0
+      rec.front_face = false;
+      b200::leaf_tag::last_hit_id() = -1;
+      bool ok = s->world->hit(r, interval(tmin, tmax), rec);
+      if (prim) prim[i] = ok ? b200::leaf_tag::last_hit_id() : -1;
+      if (t) t[i] = ok ? rec.t : 0.0;
+      if (uv) uv[2 * i] = ok ? rec.u : 0.0, uv[2 * i + 1] = ok ? rec.v : 0.0;
+      if (front) front[i] = ok ? (rec.front_face ? 1 : 0) : 0;
+      for (int c = 0; c < 3; c++) {
+        if (p) p[3 * i + c] = ok ? rec.p.e[c] : 0.0;
+        if (normal) normal[3 * i + c] = ok ? rec.normal.e[c] : 0.0;
+      }
     }
+  };
+  // hit() is const and the last-hit id is thread-local: without volumes (the only std::rand consumer under hit, src/volumne.h:36)
+  // rays are independent and a large batch is spread over the host threads
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  if (n < 65536 || s->desc.n_volumes > 0 || hw == 1) {
+    work(0, n);
+  } else {
+    std::vector<std::thread> pool;
+    for (unsigned k = 0; k < hw; k++) pool.emplace_back(work, n * k / hw, n * (k + 1) / hw);
+    for (auto &th : pool) th.join();
   }
   return 0;
 }
@@ -732,6 +768,84 @@ int ref_ray_color(int h, const double *rays7, size_t n, int depth, unsigned seed
     color c = s->cam.ray_color(r, *s->world, depth, s->light);
     for (int k = 0; k < 3; k++) rgb[3 * i + k] = c.e[k];
   }
+  return 0;
+}
+
+// One level of camera::ray_color below the hit test, through the reference's OWN objects, on a batch of rays, with every
+// std::rand value the level consumes logged (src/camera.h:202-240).  Per ray: world.hit (records a miss as mode -1; the
+// free-flight draws of volumes are taken but not logged), then exactly what ray_color does: mat->emitted, mat->scatter, and
+// for scatter_mode::kRandom the pdf it builds (scatter_record.pdf, or dual_pdf(hittable_pdf(light), scatter_record.pdf)),
+// generate(), value(), mat->p_scattered.
+//   rec12  : {p[3], normal[3], t, u, v, front_face, material row of the flattened description, primitive id}
+//   out16  : {mode, emitted[3], attenuation[3], direction[3], pdf_value, p_scattered, weight[3], 0}  (layout of b200rt_scatter)
+//   draws  : n x max_draws random_double values in consumption order; counts[i] = how many
+int ref_scatter_logged(int h, const double *rays7, size_t n, unsigned seed, double *rec12, double *out16, double *draws, int max_draws, int32_t *counts) {
+  scene *s = get(h);
+  if (!s) return -1;
+  g_rng_mode = 0;
+  srand(seed);
+  std::vector<int> log;
+  for (size_t i = 0; i < n; i++) {
+    const double *q = rays7 + 7 * i;
+    ray r(point3(q[0], q[1], q[2]), vec3(q[3], q[4], q[5]), q[6]);
+    double *hr = rec12 + 12 * i, *o = out16 + 16 * i;
+    for (int k = 0; k < 12; k++) hr[k] = 0;
+    for (int k = 0; k < 16; k++) o[k] = 0;
+    for (int k = 0; k < max_draws; k++) draws[i * max_draws + k] = 0;
+    counts[i] = 0;
+    hit_record record;
+    record.t = 0, record.u = record.v = 0, record.front_face = false;
+    b200::leaf_tag::last_hit_id() = -1;
+    if (!s->world->hit(r, interval(0.001, infinity), record)) {
+      o[0] = -1;
+      continue;
+    }
+    auto row = s->flat.mat_rows_.find(record.mat.get());
+    if (row == s->flat.mat_rows_.end()) {
+      t_err = "ref_scatter_logged: hit a material the flattener has not seen";
+      return -2;
+    }
+    for (int c = 0; c < 3; c++) hr[c] = record.p.e[c], hr[3 + c] = record.normal.e[c];
+    hr[6] = record.t, hr[7] = record.u, hr[8] = record.v, hr[9] = record.front_face ? 1.0 : 0.0;
+    hr[10] = row->second, hr[11] = b200::leaf_tag::last_hit_id();
+    log.clear();
+    t_rand_log = &log;
+    color emitted = record.mat->emitted(r, record, record.u, record.v, record.p); // src/camera.h:205
+    scatter_record srec;
+    color weight(0);
+    if (!record.mat->scatter(r, record, srec)) { // :209
+      o[0] = 0;
+    } else if (srec.mode == scatter_mode::kDetermined) { // :212-216
+      o[0] = 1;
+      for (int c = 0; c < 3; c++) o[4 + c] = srec.attenuation.e[c], o[7 + c] = srec.ray_scattered.direction().e[c];
+      weight = srec.attenuation;
+    } else {
+      o[0] = 2;
+      vec3 dir;
+      double pdf_value;
+      if (s->light == nullptr) { // :219-222
+        auto pdf = srec.pdf;
+        dir = pdf->generate();
+        pdf_value = pdf->value(dir);
+      } else { // :229-234
+        auto p0 = std::make_shared<hittable_pdf>(*s->light, record.p);
+        auto p1 = srec.pdf;
+        dual_pdf dual(p0, p1);
+        dir = dual.generate();
+        pdf_value = dual.value(dir);
+      }
+      ray scattered_ray(record.p, dir, r.time());
+      double p_scattered = record.mat->p_scattered(r, record, scattered_ray); // :225, :237
+      for (int c = 0; c < 3; c++) o[4 + c] = srec.attenuation.e[c], o[7 + c] = dir.e[c];
+      o[10] = pdf_value, o[11] = p_scattered;
+      weight = (srec.attenuation * p_scattered) / pdf_value; // the factor on input_color in :227 / :239, input_color taken as 1
+    }
+    t_rand_log = nullptr;
+    for (int c = 0; c < 3; c++) o[1 + c] = emitted.e[c], o[12 + c] = weight.e[c];
+    counts[i] = (int32_t)log.size();
+    for (int k = 0; k < max_draws && k < (int)log.size(); k++) draws[i * max_draws + k] = log[k] / (RAND_MAX + 1.0);
+  }
+  t_rand_log = nullptr;
   return 0;
 }
 
@@ -835,6 +949,20 @@ double ref_render_stock(int h, unsigned seed, int spp, const char *ppm_path, dou
     for (size_t i = 0; i < cam.image_.size(); i++)
       for (int k = 0; k < 3; k++) rgb_linear[3 * i + k] = cam.image_[i].e[k];
   return secs;
+}
+
+// The output stage of camera::render on caller-supplied pixel colours: the header lines of src/camera.h:149-151 and the
+// reference's own write_color (src/color.h:22-36) once per pixel, into memory.  Returns the length (the text is truncated to cap).
+size_t ref_write_colors(const double *rgb, int W, int H, char *out, size_t cap) {
+  std::ostringstream os;
+  int max = 255;
+  os << "P3\n";
+  os << W << ' ' << H << '\n';
+  os << max << '\n';
+  for (size_t i = 0; i < (size_t)W * H; i++) write_color(os, color(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]));
+  const std::string t = os.str();
+  if (out && cap) std::memcpy(out, t.data(), std::min(cap, t.size()));
+  return t.size();
 }
 
 // b200::render(cam, out, world, light) — the binding of INTEGRATION.md — in place of cam.render(out, world, light).

@@ -186,3 +186,37 @@ def _generate_rays_logged(self, seed, spp=1, max_draws=40):
 
 
 RefScene.generate_rays_logged = _generate_rays_logged
+
+
+def _scatter_logged(self, rays, seed=5, max_draws=8):
+    """One level of ray_color below the hit test through the reference's own objects (ref_scatter_logged).
+    -> dict(rec12, out16, draws, counts); out16[:, 0] == -1 where the ray missed."""
+    rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 7)
+    n = len(rays)
+    rec = np.zeros((n, 12), np.float64)
+    out = np.zeros((n, 16), np.float64)
+    draws = np.zeros((n, max_draws), np.float64)
+    counts = np.zeros(n, np.int32)
+    L = lib()
+    L.ref_scatter_logged.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    rc = L.ref_scatter_logged(self.h, rays.ctypes.data, n, seed, rec.ctypes.data, out.ctypes.data, draws.ctypes.data, max_draws, counts.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("ref_scatter_logged: " + L.ref_last_error().decode())
+    assert counts.max(initial=0) <= max_draws
+    return dict(rec12=rec, out16=out, draws=draws, counts=counts)
+
+
+RefScene.scatter_logged = _scatter_logged
+
+
+def write_colors(rgb):
+    """P3 text of an (H, W, 3) linear image through the reference's own write_color (src/color.h:22-36) -> bytes."""
+    rgb = np.ascontiguousarray(rgb, dtype=np.float64)
+    H, W = rgb.shape[:2]
+    L = lib()
+    L.ref_write_colors.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
+    L.ref_write_colors.restype = C.c_size_t
+    n = L.ref_write_colors(rgb.ctypes.data, W, H, None, 0)
+    buf = np.empty(n, np.uint8)
+    L.ref_write_colors(rgb.ctypes.data, W, H, buf.ctypes.data, n)
+    return buf.tobytes()

@@ -17,7 +17,7 @@ Scene = pkg.scene.Scene
 
 ALL_SCENES = sorted(f[:-4] for f in os.listdir(GOLDEN) if f.endswith(".npz"))
 CONFIG_SCENES = ["cornell", "rtow", "rtnw", "fox"]  # BASELINE.json configs[0..3]; configs[4] (Sponza) is built procedurally
-VOLUME_SCENES = {"rtnw", "cornell_volume"}
+VOLUME_SCENES = {"rtnw", "cornell_volume", "zoo_nolight", "zoo_quad", "zoo_sphere"}
 
 
 def pytest_configure(config):
@@ -82,3 +82,64 @@ def z_scores(sum_a, sumsq_a, n_a, sum_b, sumsq_b, n_b):
     with np.errstate(divide="ignore", invalid="ignore"):
         z = np.where(se > 0, (mean_a - mean_b) / se, 0.0)
     return z, mean_a, mean_b
+
+
+def map_scatter_draws(scene, rec12, mode, draws, counts, quad_random_swapped=True):
+    """The std::rand values one level of ray_color consumed (reference consumption order, as logged by
+    oracle/ref_harness.cc: ref_scatter_logged) -> the draws6 = {m0 m1 m2 s0 s1 s2} addressing of b200rt_scatter.
+
+    Consumption order in the reference: material::scatter first (metal: u1, u2 of random_in_unit_sphere, src/material.h:87;
+    dielectric: one value unless total internal reflection short-circuits it, :123; gloss: the specular test, then r1, r2 of
+    random_cosine_direction when specular, :161-163), then for kRandom the pdf: dual_pdf's choice when a light was passed
+    (src/pdf.h:53), then the pair of generate().  quad::random writes `random_double() * u_ + random_double() * v_` in ONE
+    expression (src/quad.h:76): the order of the two calls is the compiler's; g++ 13 -O2 calls the one multiplying v_ first
+    (established by test_scatter_draw_order_of_quad_random)."""
+    n = len(rec12)
+    out = np.zeros((n, 6))
+    kinds = scene.materials["kind"][rec12[:, 10].astype(int)]
+    has_light = scene.light_kind != abi.LIGHT_NONE
+    for i in range(n):
+        if mode[i] < 0:
+            continue
+        log = list(draws[i, : counts[i]])
+        k = kinds[i]
+        if k == abi.MAT_METAL:
+            out[i, 1:3] = log[0:2]
+            log = log[2:]
+        elif k == abi.MAT_DIELECTRIC:
+            if log:
+                out[i, 0] = log[0]
+            else:
+                out[i, 0] = 0.5  # never read: total internal reflection decided it
+            log = log[1:]
+        elif k == abi.MAT_GLOSS:
+            out[i, 0] = log[0]
+            log = log[1:]
+            if mode[i] == 1:
+                out[i, 1:3] = log[0:2]
+                log = log[2:]
+        if mode[i] == 2:
+            if has_light:
+                out[i, 3] = log[0]
+                log = log[1:]
+                pair = log[0:2]
+                if out[i, 3] < 0.5 and scene.light_kind == abi.LIGHT_QUAD and quad_random_swapped:
+                    pair = pair[::-1]
+            else:
+                pair = log[0:2]
+            out[i, 4:6] = pair
+            log = log[2:]
+        assert not log, (i, k, mode[i], counts[i])
+    return out
+
+
+def scatter_keep(g):
+    """Records of the golden scatter batch that can be compared: the ray hit something, and - for value_noise textures, whose
+    lattice lookup has no bounds check (src/noise.h:109-116: points on the last lattice cell read past the array, in the
+    reference and in any faithful restatement) - the hit point lies inside the lattice."""
+    ref, rec = g["scatter_out16"], g["scatter_rec12"]
+    keep = ref[:, 0] >= 0
+    if len(g.scene.value_noise):
+        res = int(g.scene.value_noise["resolution"].min())
+        keep &= ((rec[:, 0:3] >= 0) & (rec[:, 0:3] < res - 2)).all(axis=1)
+    return keep

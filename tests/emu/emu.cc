@@ -106,6 +106,35 @@ int emu_texture_sample(void *h, int tex, const double *uvp5, size_t n, double *r
   return 0;
 }
 
+// the body of k_scatter (shade_kernels.cuh): shade_hit on supplied records and supplied draws
+int emu_scatter(void *h, const double *rays7, const double *rec12, const double *draws6, size_t n, double *out16) {
+  const DevScene &S = static_cast<EmuScene *>(h)->S;
+  for (size_t i = 0; i < n; i++) {
+    const double *q = rays7 + 7 * i, *hr = rec12 + 12 * i, *u = draws6 + 6 * i;
+    const Ray r{v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6]};
+    Rec rec;
+    rec.p = v3(hr[0], hr[1], hr[2]), rec.normal = v3(hr[3], hr[4], hr[5]);
+    rec.t = hr[6], rec.u = hr[7], rec.v = hr[8];
+    rec.front_face = hr[9] != 0.0;
+    rec.mat = (int)hr[10];
+    rec.prim = -1;
+    FixedDraws fd;
+    fd.m = Draws{u[0], u[1], u[2], 0.0};
+    fd.s = Draws{u[3], u[4], u[5], 0.0};
+    ScatterDetail det;
+    const Scatter sc = shade_hit<-1, FixedDraws>(S, rec, r, fd, 0, &det);
+    double *o = out16 + 16 * i;
+    o[0] = (double)det.mode;
+    o[1] = det.emitted.x, o[2] = det.emitted.y, o[3] = det.emitted.z;
+    o[4] = det.attenuation.x, o[5] = det.attenuation.y, o[6] = det.attenuation.z;
+    o[7] = sc.dir.x, o[8] = sc.dir.y, o[9] = sc.dir.z;
+    o[10] = det.pdf_value, o[11] = det.p_scattered;
+    const V w = det.mode == 0 ? v3(0, 0, 0) : sc.value;
+    o[12] = w.x, o[13] = w.y, o[14] = w.z, o[15] = 0.0;
+  }
+  return 0;
+}
+
 // per-sample radiance, one path at a time, with the update rule of k_shade (shade_kernels.cuh)
 int emu_render(void *h, int mirror, const b200rt_camera *c, uint64_t seed, int spp_begin, int spp_end, int kill_zero, double *rgb_sum,
                double *per_sample, uint64_t *rays_out) {

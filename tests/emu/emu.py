@@ -42,6 +42,7 @@ def lib():
         L.emu_trace.argtypes = [vp, i32, vp, sz, dbl, dbl, u64, vp, vp, vp, vp, vp, vp]
         L.emu_generate_rays.argtypes = [C.POINTER(abi.Camera), u64, i32, i32, vp]
         L.emu_texture_sample.argtypes = [vp, i32, vp, sz, vp]
+        L.emu_scatter.argtypes = [vp, vp, vp, vp, sz, vp]
         L.emu_render.argtypes = [vp, i32, C.POINTER(abi.Camera), u64, i32, i32, i32, vp, vp, vp]
         _lib = L
     return _lib
@@ -73,6 +74,14 @@ class EmuScene:
         rgb = np.zeros((len(uvp), 3))
         lib().emu_texture_sample(self.h, tex, uvp.ctypes.data, len(uvp), rgb.ctypes.data)
         return rgb
+
+    def scatter(self, rays, rec12, draws6):
+        rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 7)
+        rec12 = np.ascontiguousarray(rec12, dtype=np.float64).reshape(-1, 12)
+        draws6 = np.ascontiguousarray(draws6, dtype=np.float64).reshape(-1, 6)
+        out = np.zeros((len(rays), 16))
+        lib().emu_scatter(self.h, rays.ctypes.data, rec12.ctypes.data, draws6.ctypes.data, len(rays), out.ctypes.data)
+        return out
 
     def render(self, camera, seed, spp_begin, spp_end, mirror=False, kill_zero=False):
         H, W = camera.image_height, camera.image_width

@@ -3,7 +3,7 @@ with g++ behind stand-ins for the CUDA built-ins) against the reference's golden
 this pins the host logic (flattener, BVH builder, fp32 conservative box filter, tie-break by reference order) without a GPU."""
 import numpy as np
 import pytest
-from conftest import ALL_SCENES, VOLUME_SCENES, golden, same
+from conftest import ALL_SCENES, VOLUME_SCENES, golden, map_scatter_draws, same, scatter_keep
 
 import emu
 
@@ -77,3 +77,22 @@ def test_emu_render_equals_oracle(emu_lib, name, build_oracle):
     close = np.abs(a["sum"] - b["sum"]) <= 1e-9 * np.maximum(np.abs(b["sum"]), 1e-3)  # sincos / fused libm calls may differ in the last place
     assert close.mean() > 0.995, close.mean()
     assert abs(a["rays"] - b["stats"]["rays"]) <= 0.002 * b["stats"]["rays"] + 2
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_emu_shading_on_reference_draws(emu_lib, name):
+    """The DEVICE shading function (csrc/shading.cuh: shade_hit, as k_scatter calls it) executed on the CPU, on the reference's
+    own hit records and the std::rand values it consumed: identical to what the reference's material / pdf objects produced
+    (here both sides use glibc's libm, so even the sincos / pow paths must agree to the last bit, except where the device code
+    deliberately shares work: sincos() instead of separate sin() and cos())."""
+    g = golden(name)
+    ref, rec = g["scatter_out16"], g["scatter_rec12"]
+    keep = scatter_keep(g)
+    d6 = map_scatter_draws(g.scene, rec, ref[:, 0], g["scatter_draws"], g["scatter_counts"])
+    out = emu_lib.EmuScene(g.scene).scatter(g["scatter_rays"][keep], rec[keep], d6[keep])
+    ref = ref[keep]
+    assert np.array_equal(out[:, 0], ref[:, 0])
+    assert same(out[:, 1:7], ref[:, 1:7]).all(), "emitted / attenuation"
+    close = np.isclose(out[:, 7:15], ref[:, 7:15], rtol=1e-13, atol=1e-15) | same(out[:, 7:15], ref[:, 7:15])
+    assert close.all(), f"{name}: {(~close).any(axis=1).sum()} records differ"
+    assert same(out[:, 7:15], ref[:, 7:15]).all(axis=1).mean() > 0.9

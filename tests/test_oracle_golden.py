@@ -3,7 +3,7 @@ tests/golden/ (made by tools/make_golden.py).  This is what pins the oracle: hit
 lookups must be bit-identical; images must agree statistically (different random streams)."""
 import numpy as np
 import pytest
-from conftest import ALL_SCENES, VOLUME_SCENES, golden, same, z_scores
+from conftest import ALL_SCENES, VOLUME_SCENES, golden, map_scatter_draws, same, scatter_keep, z_scores
 
 
 @pytest.mark.parametrize("name", ALL_SCENES)
@@ -57,3 +57,38 @@ def test_image_statistics(name, build_oracle):
     # rays per sample (definition of SURVEY.md §8d) agree within 2 %
     rps_o, rps_r = r["stats"]["rays"] / r["stats"]["samples"], int(g["ref_rays_count"]) / int(g["ref_samples"])
     assert abs(rps_o - rps_r) < 0.02 * rps_r + 0.01
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_shading_bit_exact_on_reference_draws(name, build_oracle):
+    """One level of ray_color below the hit test (material::emitted / scatter, the pdf the reference builds, generate / value,
+    p_scattered; src/camera.h:202-240) replayed on the std::rand values the reference itself consumed: mode, emission,
+    attenuation, scattered direction, pdf value, p_scattered and the weight on the incoming radiance are bit-identical."""
+    g = golden(name)
+    ref, rec = g["scatter_out16"], g["scatter_rec12"]
+    hit = scatter_keep(g)
+    d6 = map_scatter_draws(g.scene, rec, ref[:, 0], g["scatter_draws"], g["scatter_counts"])
+    out = build_oracle.scatter(g.scene, g["scatter_rays"][hit], rec[hit], d6[hit])
+    ok = same(out, ref[hit])
+    assert ok.all(), f"{name}: {(~ok).any(axis=1).sum()} of {hit.sum()} records differ (columns {np.unique(np.nonzero(~ok)[1]).tolist()})"
+    assert hit.sum() > 200
+
+
+def test_scatter_draw_order_of_quad_random(build_oracle):
+    """quad::random (src/quad.h:76) calls random_double() twice inside one expression; which call runs first is the compiler's
+    choice.  The reference binary built here calls the factor of v_ first: the straight mapping must FAIL, the swapped one pass
+    (a reminder to re-establish the order if the compiler changes; the distribution is the same either way)."""
+    g = golden("zoo_quad")
+    ref, rec = g["scatter_out16"], g["scatter_rec12"]
+    hit = ref[:, 0] >= 0
+    straight = map_scatter_draws(g.scene, rec, ref[:, 0], g["scatter_draws"], g["scatter_counts"], quad_random_swapped=False)
+    out = build_oracle.scatter(g.scene, g["scatter_rays"][hit], rec[hit], straight[hit])
+    assert not same(out, ref[hit]).all()
+
+
+@pytest.mark.parametrize("name,kind", [("zoo_nolight", 0), ("zoo_quad", 1), ("zoo_sphere", 2)])
+def test_zoo_scenes_cover_every_material_under_every_light_kind(name, kind):
+    g = golden(name)
+    assert g.scene.light_kind == kind
+    kinds = g.scene.materials["kind"][g["scatter_rec12"][g["scatter_out16"][:, 0] >= 0][:, 10].astype(int)]
+    assert set(np.unique(kinds).tolist()) == {0, 1, 2, 3, 4, 5}

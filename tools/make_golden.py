@@ -27,6 +27,8 @@ SCENES = {
     "cornell_specular": (40, 256), "perlin_ball": (40, 128), "light_earth": (48, 256), "skybox_fisheye": (40, 256),
     "fuzz_metal": (57, 256), "white_sphere": (40, 128), "motion_ball": (48, 64),
     "noise_perlin": (40, 16), "noise_value": (40, 16), "noise_worley": (40, 16), "noise_voronoi": (40, 16),
+    # every material under each kind of `light` argument (none / quad / sphere: src/quad.h:66-78, src/sphere.h:76-81)
+    "zoo_nolight": (48, 256), "zoo_quad": (48, 256), "zoo_sphere": (48, 256),
 }
 
 
@@ -65,8 +67,30 @@ def aimed_rays(rs, rng, n=768):
     return rays
 
 
+def scatter_vectors(rs, rays):
+    """One level of ray_color below the hit test through the reference's own material / pdf objects, with the std::rand values
+    it consumed (oracle/ref_harness.cc: ref_scatter_logged), on every third ray of the hit batch."""
+    sub = rays[::3]
+    g = rs.scatter_logged(sub, seed=5, max_draws=8)
+    return dict(scatter_rays=sub, scatter_rec12=g["rec12"], scatter_out16=g["out16"], scatter_draws=g["draws"], scatter_counts=g["counts"])
+
+
+def add_scatter(name, width):
+    """Adds the scatter vectors to an existing golden file, leaving everything else in it untouched."""
+    path = os.path.join(OUT, name + ".npz")
+    z = dict(np.load(path))
+    rs = R.RefScene(name, width=width)
+    assert rs.scene.nodes.tobytes() == z["nodes"].tobytes(), "the scene built now must be the scene stored then"
+    z.update(scatter_vectors(rs, z["trace_rays"]))
+    np.savez_compressed(path, **z)
+    m = z["scatter_out16"][:, 0]
+    print(f"{name:20s} scatter vectors: {len(m)} rays, modes {np.bincount((m + 1).astype(int), minlength=4).tolist()} (miss / none / determined / random)")
+
+
 def make(name, width, spp):
-    rng = np.random.RandomState(abs(hash(name)) % (2**31))
+    import zlib
+
+    rng = np.random.RandomState(zlib.crc32(name.encode()) % (2**31))
     full = R.RefScene(name)
     rs = R.RefScene(name, width=width)
     assert full.scene.nodes.tobytes() == rs.scene.nodes.tobytes(), "scene must not depend on the camera"
@@ -79,6 +103,7 @@ def make(name, width, spp):
     extra["trace_rays"] = tr
     for k, v in h.items():
         extra["trace_" + k] = v
+    extra.update(scatter_vectors(rs, tr))
     # textures
     nt = len(rs.scene.textures)
     uvp = np.concatenate([rng.rand(64 * nt, 2), rng.uniform(-30, 600, size=(64 * nt, 3))], axis=1)
@@ -103,7 +128,81 @@ def make(name, width, spp):
           f"render={st['seconds']:.1f}s")
 
 
+def make_write_color():
+    """tests/golden/aux/write_color.npz: linear images and the bytes the reference's own output stage wrote for them.
+    (a) a stock camera::render of a small Cornell box: cam.image_ and the P3 file it wrote (src/camera.h:149-151, 174);
+    (b) crafted values through write_color (src/color.h:16-36): negative, zero, denormal, > 1, huge, inf, NaN, and values
+        next to every integer boundary of int(255.999 * pow(c, 1/2.2))."""
+    import tempfile
+
+    rs = R.RefScene("cornell", width=20, spp=4, depth=6)
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "stock.ppm")
+        _, img = rs.render_stock(spp=4, seed=1, ppm_path=path)
+        stock_text = open(path, "rb").read()
+    assert stock_text == R.write_colors(img), "camera::render's file is its header + write_color per pixel"
+    rng = np.random.RandomState(7)
+    k = np.arange(0, 300)
+    edges = (k / 255.999) ** 2.2  # pow(c, 1/2.2) * 255.999 lands next to the integer k
+    vals = np.concatenate([edges, np.nextafter(edges, 0), np.nextafter(edges, 1e9), edges * (1 - 1e-12), edges * (1 + 1e-12),
+                           rng.rand(2000), 10 ** rng.uniform(-12, 6, 2000), -rng.rand(50),
+                           [0.0, -0.0, 5e-324, 1e-310, 1.0, 2.0**31, 1e300, np.inf, -np.inf, np.nan, 255.0, 1e9, 8.4e6]])
+    n = len(vals) // 3 * 3
+    crafted = rng.permutation(vals[:n]).reshape(1, n // 3, 3)
+    text = R.write_colors(crafted)
+    out = os.path.join(OUT, "aux")
+    os.makedirs(out, exist_ok=True)
+    np.savez_compressed(os.path.join(out, "write_color.npz"), stock_image=img, stock_text=np.frombuffer(stock_text, np.uint8),
+                        crafted_image=crafted, crafted_text=np.frombuffer(text, np.uint8))
+    print(f"write_color: stock {img.shape} {len(stock_text)} B, crafted {crafted.shape} {len(text)} B")
+
+
+# name -> (width, reference spp): sized so that the reference's own Monte-Carlo noise stays below ~6e-4 RMSE per channel
+CONVERGED = {"cornell": (24, 1_500_000), "rtow": (24, 300_000), "rtnw": (16, 1_600_000), "fox": (32, 100_000), "sponza16k": (16, 400_000)}
+SPONZA_SMALL = 16384  # triangles of the stand-in mesh used for the converged render: the reference's x-sorted tree needs 0.3 ms per ray on the full one
+
+
+def make_converged(name):
+    """tests/golden/aux/converged_<name>.npz: the reference's OWN high-spp render (its generate_ray + ray_color on all host threads)
+    of a BASELINE.json config at thumbnail resolution: per-pixel sum and sum of squares.  The GPU test renders the same
+    camera at 4x the samples and asserts the north-star criterion literally (per-channel RMSE < 1e-3, mean within 0.5 %)."""
+    import importlib
+
+    width, spp = CONVERGED[name]
+    if name == "sponza16k":
+        pkg = importlib.import_module("cpu-ray-tracing-implementation_b200")
+        mesh = pkg.scene.sponza_standin_triangles(SPONZA_SMALL, 7)
+        rs = R.RefScene("sponza", width=width, mesh=mesh)
+    else:
+        rs = R.RefScene(name, width=width)
+    s, q, st = rs.render(spp, seed=20261105, threads=0, rng_mode=1)
+    out = os.path.join(OUT, "aux")
+    os.makedirs(out, exist_ok=True)
+    path = os.path.join(out, f"converged_{name}.npz")
+    extra = dict(cam=np.frombuffer(rs.camera.to_bytes(), np.uint8), ref_sum=s, ref_sumsq=q, ref_spp=np.int64(spp), ref_rays_count=np.int64(st["rays"]),
+                 ref_nan_samples=np.int64(st["nan_samples"]))
+    if name == "sponza16k":
+        np.savez_compressed(path, n_triangles=np.int64(SPONZA_SMALL), mesh_seed=np.int64(7), **extra)  # the scene is procedural (scene.sponza_standin_scene)
+    else:
+        np.savez_compressed(path, **extra)  # the scene is tests/golden/<name>.npz
+    m = s / spp
+    var = np.maximum(q / spp - m * m, 0)
+    print(f"converged {name:10s} {rs.camera.image_width}x{rs.camera.image_height} {spp} spp in {st['seconds']:.0f} s: noise floor (RMSE of the reference mean) "
+          f"{np.sqrt(var.mean() / spp):.2e}, mean {m.mean():.5f}", flush=True)
+
+
 if __name__ == "__main__":
+    if "--converged" in sys.argv:
+        for n in ([a for a in sys.argv[1:] if not a.startswith("--")] or CONVERGED):
+            make_converged(n)
+        sys.exit(0)
+    if "--write-color" in sys.argv:
+        make_write_color()
+        sys.exit(0)
     os.makedirs(OUT, exist_ok=True)
-    for n in (sys.argv[1:] or SCENES):
-        make(n, *SCENES[n])
+    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    for n in (args or SCENES):
+        if "--add-scatter" in sys.argv:
+            add_scatter(n, SCENES[n][0])
+        else:
+            make(n, *SCENES[n])
