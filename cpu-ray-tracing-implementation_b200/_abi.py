@@ -16,7 +16,7 @@ MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_GLOSS, MAT_ISOTROPIC, MAT_DIFFUSE
 TEX_SOLID, TEX_CHECKER, TEX_PICTURE, TEX_PERLIN, TEX_VALUE, TEX_WORLEY, TEX_VORONOI = 0, 1, 2, 3, 4, 5, 6
 LIGHT_NONE, LIGHT_QUAD, LIGHT_SPHERE, LIGHT_DEFAULT = 0, 1, 2, 3
 CAM_PERSPECTIVE, CAM_ORTHOGRAPHIC, CAM_FISHEYE, CAM_LENS = 0, 1, 2, 3
-OPT_TRAVERSAL, OPT_WAVE_PATHS, OPT_KILL_ZERO_WEIGHT, OPT_BVH_LEAF_SIZE, OPT_RESERVED_4, OPT_REFILL_LANES, OPT_EXTEND_BLOCKS, OPT_SPECULATIVE_LEAF, OPT_FUSE_MISS, OPT_EXTEND_STAGES, OPT_SMEM_CARVEOUT, OPT_BVH_BUILDER, OPT_BVH_WIDTH, OPT_PIPELINES, OPT_PIPE_EXTEND_CTAS, OPT_TAIL_PATHS = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15
+OPT_TRAVERSAL, OPT_WAVE_PATHS, OPT_KILL_ZERO_WEIGHT, OPT_BVH_LEAF_SIZE, OPT_RESERVED_4, OPT_REFILL_LANES, OPT_EXTEND_BLOCKS, OPT_SPECULATIVE_LEAF, OPT_FUSE_MISS, OPT_EXTEND_STAGES, OPT_SMEM_CARVEOUT, OPT_BVH_BUILDER, OPT_BVH_WIDTH, OPT_PIPELINES, OPT_PIPE_EXTEND_CTAS, OPT_TAIL_PATHS, OPT_WAVE_LOOP = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16
 BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1
 TRAVERSAL_FAST, TRAVERSAL_MIRROR = 0, 1
 
@@ -164,7 +164,17 @@ EXPORTS = [
     "b200rt_texture_sample",
     "b200rt_scatter",
     "b200rt_abi_sizeof",
+    "b200rt_group_create",
+    "b200rt_group_destroy",
+    "b200rt_group_size",
+    "b200rt_group_context",
+    "b200rt_group_set_option",
+    "b200rt_group_upload_scene",
+    "b200rt_group_set_camera",
+    "b200rt_group_render",
+    "b200rt_group_reduce_backend",
 ]
+GROUP_OPT_REDUCE, GROUP_REDUCE_NCCL, GROUP_REDUCE_PEER = 1000, 0, 1
 
 
 def bind(lib):
@@ -189,8 +199,18 @@ def bind(lib):
     lib.b200rt_texture_sample.argtypes = [vp, i32, vp, sz, vp]
     lib.b200rt_scatter.argtypes = [vp, vp, vp, vp, sz, vp]
     lib.b200rt_abi_sizeof.argtypes = [i32]
+    lib.b200rt_group_create.argtypes = [C.POINTER(i32), i32, C.POINTER(vp)]
+    lib.b200rt_group_destroy.argtypes = [vp]
+    lib.b200rt_group_size.argtypes = [vp]
+    lib.b200rt_group_context.argtypes = [vp, i32, C.POINTER(vp)]
+    lib.b200rt_group_set_option.argtypes = [vp, i32, dbl]
+    lib.b200rt_group_upload_scene.argtypes = [vp, C.POINTER(SceneDesc)]
+    lib.b200rt_group_set_camera.argtypes = [vp, C.POINTER(Camera)]
+    lib.b200rt_group_render.argtypes = [vp, u64, i32, i32, vp, C.POINTER(Stats)]
+    lib.b200rt_group_reduce_backend.argtypes = []
+    lib.b200rt_group_reduce_backend.restype = C.c_char_p
     for name in EXPORTS:
-        if name not in ("b200rt_last_error", "b200rt_abi_sizeof", "b200rt_ppm_bound"):
+        if name not in ("b200rt_last_error", "b200rt_abi_sizeof", "b200rt_ppm_bound", "b200rt_group_reduce_backend"):
             getattr(lib, name).restype = C.c_int
     lib.b200rt_abi_sizeof.restype = C.c_size_t
     lib.b200rt_ppm_bound.restype = C.c_size_t

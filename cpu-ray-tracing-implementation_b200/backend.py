@@ -151,3 +151,58 @@ class Context:
         self._check(self._lib.b200rt_format_ppm(self._h, rgb_sum.ctypes.data, total_spp, buf.ctypes.data, cap, C.byref(n)))
         return buf[: n.value].tobytes()
 
+
+
+class Group:
+    """b200rt_group: the frame split by sample range across several GPUs of this box, one NCCL reduce (include/b200rt.h)."""
+
+    def __init__(self, devices):
+        self._lib = lib()
+        self._h = C.c_void_p()
+        arr = (C.c_int * len(devices))(*devices)
+        self._check(self._lib.b200rt_group_create(arr, len(devices), C.byref(self._h)))
+        self.devices = list(devices)
+        self.camera = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise B200RTError(rc, self._lib.b200rt_last_error().decode())
+
+    def close(self):
+        if self._h:
+            self._lib.b200rt_group_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_option(self, option, value):
+        self._check(self._lib.b200rt_group_set_option(self._h, option, float(value)))
+
+    def upload_scene(self, scene):
+        d, keep = scene.desc()
+        self._check(self._lib.b200rt_group_upload_scene(self._h, C.byref(d)))
+
+    def set_camera(self, camera):
+        self.camera = camera.copy()
+        self._check(self._lib.b200rt_group_set_camera(self._h, C.byref(self.camera)))
+
+    def render(self, seed, spp_begin, spp_end, out=None, want_stats=True):
+        H, W = self.camera.image_height, self.camera.image_width
+        if out is None:
+            out = np.zeros((H, W, 3), np.float64)
+        st = abi.Stats()
+        self._check(self._lib.b200rt_group_render(self._h, seed, spp_begin, spp_end, out.ctypes.data, C.byref(st) if want_stats else None))
+        return out, (st.as_dict() if want_stats else None)
+
+    def reduce_backend(self):
+        return self._lib.b200rt_group_reduce_backend().decode()

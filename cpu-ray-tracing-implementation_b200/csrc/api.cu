@@ -89,7 +89,7 @@ struct b200rt_ctx {
     DevMem mem;
     uint32_t capacity = 0;
     bool mirror = false;
-    PathBuf pool[2]{};
+    Pools pools{};
     HitRef *hits = nullptr;
     Rec *recs = nullptr;
     Queues queues{};
@@ -97,7 +97,21 @@ struct b200rt_ctx {
     WaveCtl *h_ctl = nullptr; // pinned
     cudaStream_t stream = nullptr; // pipeline stream (two-pipeline mode)
     cudaEvent_t done = nullptr;
+    // device-driven wave loop: one CUDA graph = a while node whose body is one wave; rebuilt when anything baked into its
+    // kernel nodes (scene pointers, camera, sample range, seed, accumulator, options) changes
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    std::string graph_key;
+    int graph_launches_per_wave = 0;
+    void drop_graph() {
+      if (graph_exec) cudaGraphExecDestroy(graph_exec);
+      if (graph) cudaGraphDestroy(graph);
+      graph_exec = nullptr, graph = nullptr;
+      graph_key.clear();
+    }
   } w[B200_MAX_PIPELINES];
+  cudaStream_t cap_stream = nullptr; // stream captures are recorded on (never executes anything)
+  int wave_loop = 1; // B200RT_OPT_WAVE_LOOP: 1 = device-driven CUDA-graph while loop, 0 = host-driven loop with read-backs
   cudaEvent_t ev_fork = nullptr;
   int pipelines = 2;        // measured: +4 % on RTOW, +5 % on the Sponza stand-in over one pipeline (profiles/r01_r_pipelines.txt)
   int pipe_extend_ctas = 4; // fewer (leaving registers for the other half's kernels) is slower: extend needs its occupancy
@@ -276,6 +290,8 @@ int b200rt_create(int device, b200rt_ctx **out) {
   CU(cudaEventCreate(&c->ev0));
   CU(cudaEventCreate(&c->ev1));
   CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  CU(cudaStreamCreateWithFlags(&c->cap_stream, cudaStreamNonBlocking));
+  if (const char *e = getenv("B200RT_WAVE_LOOP")) c->wave_loop = atoi(e) != 0; // debugging aid: default of B200RT_OPT_WAVE_LOOP
   for (auto &w : c->w) {
     CU(cudaMallocHost(&w.h_ctl, sizeof(WaveCtl)));
     CU(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
@@ -292,12 +308,14 @@ int b200rt_destroy(b200rt_ctx *c) {
   c->scene_mem.release();
   for (auto &w : c->w) {
     if (w.stream) cudaStreamSynchronize(w.stream);
+    w.drop_graph();
     w.mem.release();
     if (w.h_ctl) cudaFreeHost(w.h_ctl);
     if (w.done) cudaEventDestroy(w.done);
     if (w.stream) cudaStreamDestroy(w.stream);
   }
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->cap_stream) cudaStreamDestroy(c->cap_stream);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -351,6 +369,10 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
   case B200RT_OPT_SMEM_CARVEOUT:
     if (!(value >= -1 && value <= 100)) return fail(B200RT_ERR_INVALID, "carve-out must be -1 (automatic) or a percentage");
     c->carveout_pct = (int)value;
+    return B200RT_OK;
+  case B200RT_OPT_WAVE_LOOP:
+    if (value != 0 && value != 1) return fail(B200RT_ERR_INVALID, "wave loop must be 0 (host-driven) or 1 (device-driven CUDA graph)");
+    c->wave_loop = (int)value;
     return B200RT_OK;
   case B200RT_OPT_REFILL_LANES:
     if (!(value >= 0 && value <= 32)) return fail(B200RT_ERR_INVALID, "refill lanes must be in [0, 32] (0 = automatic)");
@@ -638,12 +660,13 @@ namespace {
 
 int ensure_wave(b200rt_ctx::WaveSet &w, uint32_t capacity, bool mirror) {
   if (w.capacity >= capacity && (!mirror || w.mirror)) return B200RT_OK;
+  w.drop_graph(); // its kernel nodes point into the pools that are about to be freed
   w.mem.release();
   w.capacity = 0;
   auto col = [&](void **p, size_t elem) { return w.mem.alloc(p, (size_t)capacity * elem); };
   for (int b = 0; b < 2; b++) {
-    CU(col((void **)&w.pool[b].base, B200_PATH_QUADS * sizeof(double2)));
-    w.pool[b].capacity = capacity;
+    CU(col((void **)&w.pools.b[b].base, B200_PATH_QUADS * sizeof(double2)));
+    w.pools.b[b].capacity = capacity;
   }
   CU(col((void **)&w.hits, sizeof(HitRef)));
   w.recs = nullptr;
@@ -658,18 +681,18 @@ int ensure_wave(b200rt_ctx::WaveSet &w, uint32_t capacity, bool mirror) {
 // Persistent extend launch.  The shared-memory carve-out is requested explicitly (smallest configuration that holds the
 // resident CTAs): what is left of the 256 KB is the L1 that caches BVH nodes and primitives.
 template <class K>
-void launch_extend(K kernel, b200rt_ctx *c, b200rt_ctx::WaveSet &w, int ctas_per_sm, int threads, int smem_per_cta, cudaStream_t s, const PathBuf &cur, const WaveParams &wp) {
+void launch_extend(K kernel, b200rt_ctx *c, b200rt_ctx::WaveSet &w, int ctas_per_sm, int threads, int smem_per_cta, cudaStream_t s, const Pools &cur, const WaveParams &wp) {
   const int want_kb = (ctas_per_sm * (smem_per_cta + 1024) + 1023) / 1024;
   cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, c->carveout_pct >= 0 ? c->carveout_pct : std::min(100, (want_kb * 100 + 227) / 228));
   kernel<<<c->sm_count * ctas_per_sm, threads, 0, s>>>(w.ctl, c->S, cur, w.hits, wp);
 }
 
 template <bool MIRROR>
-int launch_shades(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, int grid, const PathBuf &cur, const PathBuf &nxt, double *accum, const WaveParams &wp) {
+int launch_shades(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, int grid, const Pools &pools, double *accum, const WaveParams &wp) {
   int n = 0;
 #define SHADE(K)                                                                                                       \
   if (K == B200_Q_MISS ? wp.fused_miss == 0 : (c->kinds_present >> K & 1u))                                                                \
-  n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(w.ctl, c->S, cur, nxt, w.hits, w.recs, w.queues.q[K], accum, wp)
+  n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(w.ctl, c->S, pools, w.hits, w.recs, w.queues.q[K], accum, wp)
   SHADE(B200_Q_MISS);
   SHADE(B200RT_MAT_DIFFUSE_LIGHT);
   SHADE(B200RT_MAT_LAMBERTIAN);
@@ -684,10 +707,12 @@ int launch_shades(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, int gri
 // One wave of one pipeline on stream s: generate -> extend -> classify -> shade per queue -> roll the counters over.
 // Returns the number of launches (negative: error).  ext_ctas = resident extend CTAs per SM (4 alone; fewer when a second
 // pipeline's shade kernels are meant to run beside it).  ext_events (may be NULL) receives an event pair around extend.
-int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned long long wave, const DevCamera &cam, const WaveParams &wp, int g_gen, int g_ext,
-                double *d_rgb_sum, int ext_ctas, std::vector<cudaEvent_t> *ext_events) {
+// `more` (may be 0): the conditional handle of the graph while loop this wave is being captured into; the last kernel then
+// also decides whether the loop goes round again.
+int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, const DevCamera &cam, const WaveParams &wp, int g_gen, int g_ext,
+                double *d_rgb_sum, int ext_ctas, std::vector<cudaEvent_t> *ext_events, cudaGraphConditionalHandle more = 0) {
   const bool mirror = c->traversal == B200RT_TRAVERSAL_MIRROR;
-  const PathBuf &cur = w.pool[wave & 1], &nxt = w.pool[(wave & 1) ^ 1];
+  const Pools &cur = w.pools; // which pool holds this wave is decided on the device (WaveCtl::waves & 1)
   const bool compact = cam.c.mode == B200RT_CAM_FISHEYE; // the only camera with samples that produce no ray
   int n_gen_launches = 2;
   if (compact) {
@@ -736,10 +761,55 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
     }
   if (ext_events) CU(cudaEventRecord(ext_events->back(), s));
   if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(w.ctl, w.hits, w.queues);
-  const int n_shade = mirror ? launch_shades<true>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp) : launch_shades<false>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp);
-  k_ctl_swap<<<1, 1, 0, s>>>(w.ctl);
+  const int n_shade = mirror ? launch_shades<true>(c, w, s, g_ext, cur, d_rgb_sum, wp) : launch_shades<false>(c, w, s, g_ext, cur, d_rgb_sum, wp);
+  if (more)
+    k_ctl_swap_cond<<<1, 1, 0, s>>>(w.ctl, more);
+  else
+    k_ctl_swap<<<1, 1, 0, s>>>(w.ctl);
   return (mirror ? 2 : 3) + (tail ? 1 : 0) + n_gen_launches + n_shade;
 }
+
+// The device-driven wave loop of one pipeline as a CUDA graph: a single conditional WHILE node whose body is one wave
+// (captured from launch_wave) and whose last kernel, k_ctl_swap_cond, sets the loop condition from the device-side counters.
+// Everything a kernel node bakes in goes into `key`; an unchanged key re-launches the instantiated graph as it is.
+int ensure_wave_graph(b200rt_ctx *c, b200rt_ctx::WaveSet &w, const std::string &key, const DevCamera &cam, const WaveParams &wp, int g_gen, int g_ext,
+                      double *d_rgb_sum, int ext_ctas) {
+  if (w.graph_exec && w.graph_key == key) return B200RT_OK;
+  w.drop_graph();
+  CU(cudaGraphCreate(&w.graph, 0));
+  cudaGraphConditionalHandle more;
+  CU(cudaGraphConditionalHandleCreate(&more, w.graph, 1, cudaGraphCondAssignDefault)); // every launch starts with "go round"
+  cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
+  np.type = cudaGraphNodeTypeConditional;
+  np.conditional.handle = more;
+  np.conditional.type = cudaGraphCondTypeWhile;
+  np.conditional.size = 1;
+  cudaGraphNode_t node;
+  CU(cudaGraphAddNode(&node, w.graph, nullptr, 0, &np));
+  cudaGraph_t body = np.conditional.phGraph_out[0];
+  CU(cudaStreamBeginCaptureToGraph(c->cap_stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+  const int n = launch_wave(c, w, c->cap_stream, cam, wp, g_gen, g_ext, d_rgb_sum, ext_ctas, nullptr, more);
+  cudaGraph_t captured = nullptr;
+  const cudaError_t e_end = cudaStreamEndCapture(c->cap_stream, &captured);
+  if (n < 0) {
+    w.drop_graph();
+    return n;
+  }
+  if (e_end != cudaSuccess) {
+    w.drop_graph();
+    return fail(B200RT_ERR_CUDA, "capturing the wave graph: %s", cudaGetErrorString(e_end));
+  }
+  const cudaError_t e_inst = cudaGraphInstantiate(&w.graph_exec, w.graph, 0);
+  if (e_inst != cudaSuccess) {
+    w.drop_graph();
+    return fail(B200RT_ERR_CUDA, "instantiating the wave graph: %s", cudaGetErrorString(e_inst));
+  }
+  w.graph_key = key;
+  w.graph_launches_per_wave = n;
+  return B200RT_OK;
+}
+
+template <class T> void key_add(std::string &k, const T &v) { k.append(reinterpret_cast<const char *>(&v), sizeof v); }
 
 } // namespace
 
@@ -805,6 +875,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     }
   }
 
+  const bool use_graph = c->wave_loop == 1 && !mirror;
   // Whatever happens below (a failed launch, a failed copy), the forked pipeline streams are joined back into the caller's
   // stream and the per-launch timing events are destroyed: the caller may keep using `s` and d_rgb_sum after an error.
   struct WaveLoopGuard {
@@ -841,10 +912,28 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     launches++;
     next_check = std::max(next_check, (tot[p] + cap[p] - 1) / cap[p]);
   }
+  if (use_graph) {
+    // device-driven: one graph launch per pipeline; the while node repeats the wave until the counters say the frame is done
+    for (int p = 0; p < n_pipe; p++) {
+      std::string key;
+      key_add(key, c->S), key_add(key, cam), key_add(key, wp[p]), key_add(key, cap[p]), key_add(key, d_rgb_sum), key_add(key, ext_ctas);
+      key_add(key, c->tail_paths), key_add(key, c->extend_blocks), key_add(key, c->speculative), key_add(key, c->extend_stages), key_add(key, c->carveout_pct);
+      key_add(key, c->kinds_present), key_add(key, c->w[p].pools), key_add(key, c->w[p].hits);
+      if ((rc = ensure_wave_graph(c, c->w[p], key, cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas)) != B200RT_OK) return rc;
+      CU(cudaGraphLaunch(c->w[p].graph_exec, ps[p]));
+      if (stats) CU(cudaMemcpyAsync(c->w[p].h_ctl, c->w[p].ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, ps[p]));
+    }
+    if (stats)
+      for (int p = 0; p < n_pipe; p++) {
+        CU(cudaStreamSynchronize(ps[p]));
+        launches += c->w[p].h_ctl->waves * (unsigned long long)c->w[p].graph_launches_per_wave;
+        wave = std::max(wave, c->w[p].h_ctl->waves);
+      }
+  } else
   for (;;) {
     for (int p = 0; p < n_pipe; p++) {
       if (done[p]) continue;
-      const int n = launch_wave(c, c->w[p], ps[p], wave, cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas,
+      const int n = launch_wave(c, c->w[p], ps[p], cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas,
                                 stats && n_pipe == 1 ? &ext_events : nullptr);
       if (n < 0) return n;
       launches += (unsigned long long)n;
@@ -987,3 +1076,5 @@ int b200rt_format_ppm(b200rt_ctx *c, const double *rgb_sum, int total_spp, char 
 }
 
 } // extern "C"
+
+#include "group.cuh"

@@ -23,8 +23,9 @@ DEV void prefetch_l2(const void *p) {
 #endif
 // One launch per queue.  KIND = b200rt_material_kind of every hit in the queue, or B200_Q_MISS.
 template <int KIND, bool MIRROR>
-__global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevScene S, PathBuf cur, PathBuf nxt, const HitRef *hits, const Rec *recs,
+__global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevScene S, Pools P, const HitRef *hits, const Rec *recs,
                                                 const uint32_t *queue, double *accum, WaveParams wp) {
+  const PathBuf cur = pool_cur(c, P), nxt = pool_nxt(c, P);
   // survivors are appended to the other pool with ONE global atomic per CTA iteration (same-address atomics are the
   // scarce resource of this kernel family: see k_classify); double-buffered by iteration parity
   __shared__ uint32_t s_cnt[2][4], s_base[2];
@@ -110,7 +111,8 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
 // (keyed by pixel, sample, bounce), so the contribution of every path is unchanged.  The last CTA to finish empties the
 // wave (n_cur = 0): the kernels that follow in the stream find nothing to do.  WaveCtl::tail_done counts the finished CTAs
 // (zeroed by k_ctl_init / k_ctl_generated; no other kernel touches it).
-__global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, PathBuf cur, double *accum, WaveParams wp, uint32_t limit) {
+__global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, Pools P, double *accum, WaveParams wp, uint32_t limit) {
+  const PathBuf cur = pool_cur(c, P);
   const uint32_t n = c->n_cur;
   if (n == 0 || n > limit || c->next_sample != c->total_samples) return;
   unsigned long long my_rays = 0;

@@ -55,6 +55,13 @@ DEV size_t quad_index(uint32_t capacity, int q, uint32_t i) {
 #endif
 }
 DEV const double2 *quad_ptr(const PathBuf &b, int q, uint32_t i) { return b.base + quad_index(b.capacity, q, i); }
+// The two pools of a pipeline.  Which one holds the current wave is decided ON THE DEVICE from the wave counter, so that the
+// launches of a wave are identical from wave to wave (and can be the body of a CUDA-graph while loop, api.cu).
+struct Pools {
+  PathBuf b[2];
+};
+DEV PathBuf pool_cur(const WaveCtl *c, const Pools &P) { return P.b[(int)(c->waves & 1ull)]; }
+DEV PathBuf pool_nxt(const WaveCtl *c, const Pools &P) { return P.b[(int)(c->waves & 1ull) ^ 1]; }
 
 struct WaveParams {
   uint64_t seed;
@@ -171,12 +178,27 @@ __global__ void k_ctl_swap(WaveCtl *c) {
   c->waves++;
 }
 
+// The same roll-over as the last node of the CUDA-graph while loop (api.cu): the loop runs another wave while paths are
+// alive or samples remain to be generated.
+#ifndef B200_HOST_EMU
+__global__ void k_ctl_swap_cond(WaveCtl *c, cudaGraphConditionalHandle more) {
+  unsigned long long r = 0;
+  for (int k = 0; k < 8; k++) r += c->q_count[k], c->q_count[k] = 0;
+  c->rays += r;
+  c->n_cur = c->n_next;
+  c->n_next = 0;
+  c->waves++;
+  cudaGraphSetConditional(more, (c->n_cur != 0 || c->next_sample < c->total_samples) ? 1u : 0u);
+}
+#endif
+
 // ------------------------------------------------------------------------------------------------ generate
 // COMPACT (fisheye cameras): samples outside the image circle produce no ray (NaN direction, src/camera.h:268-282) and add
 // exactly 0; they are counted and DROPPED here instead of riding through extend and classify as dead slots (56 % of the Fox
 // config's samples).  Live paths are appended behind n_cur with one atomic per CTA iteration; k_ctl_generated adds n_gen.
 template <bool COMPACT>
-__global__ void __launch_bounds__(256) k_generate(WaveCtl *c, PathBuf cur, DevCamera cam, WaveParams wp) {
+__global__ void __launch_bounds__(256) k_generate(WaveCtl *c, Pools P, DevCamera cam, WaveParams wp) {
+  const PathBuf cur = pool_cur(c, P);
   const uint32_t n_new = wave_refill(c), n_cur = c->n_cur;
   const unsigned long long g0 = c->next_sample;
   __shared__ uint32_t warp_live[8], cta_base;
@@ -248,7 +270,8 @@ DEV void classify(WaveCtl *c, const Queues &Q, uint32_t i, int which) {
 }
 
 template <bool MIRROR>
-__global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, Rec *recs, Queues Q, WaveParams wp) {
+__global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, Pools P, HitRef *hits, Rec *recs, Queues Q, WaveParams wp) {
+  const PathBuf cur = pool_cur(c, P);
   const uint32_t n = c->n_cur;
   // whole warps iterate together so that the ballots in classify() see a full mask
   for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x) {
@@ -336,7 +359,8 @@ DEV void cp_async_wait_all() {
 #define B200_EXT_DYNAMIC 4 // largest number of batches claimed per atomic; 0 = static striding (profiles/r01_v_*)
 #endif
 template <int MAXREG, bool SPEC, int WARPS, int STAGES, bool WIDE>
-__global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp) {
+__global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, Pools P, HitRef *hits, WaveParams wp) {
+  const PathBuf cur = pool_cur(c, P);
 #if B200_PATH_PAIRED
   __shared__ __align__(32) double2 stage_mem[WARPS][STAGES][224]; // warp x stage x {3 columns x 32 paths x 2 quads, then q6 of 32 paths}: 3.5 KB
 #else

@@ -231,6 +231,10 @@ typedef enum b200rt_option {
   B200RT_OPT_PIPE_EXTEND_CTAS = 14, /* tuning: resident extend CTAs per SM in two-pipeline mode (1..4, default 4; fewer leave registers for the other half's kernels and were measured slower) */
   B200RT_OPT_TAIL_PATHS = 15, /* tuning: once every sample is generated and at most this many paths are alive, one kernel follows each of them to its
                                  end instead of one wave per bounce (default 32768; 0 = off).  Same draws, same contributions */
+  B200RT_OPT_WAVE_LOOP = 16,  /* who drives the wave loop of a render call: 1 (default) = the device: one CUDA graph per pipeline whose while node repeats
+                                 the wave until no path is alive and no sample is left (no host round trip; the call returns without waiting unless
+                                 statistics are requested); 0 = the host, reading the counters back (the mode that can time single launches:
+                                 b200rt_stats::extend_ms).  The mirror traversal always uses the host loop */
   B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 8 from 32 Ki BVH nodes) */
 } b200rt_option;
 
@@ -328,6 +332,31 @@ int b200rt_texture_sample(b200rt_ctx *ctx, int tex, const double *uvp5, size_t n
  *              mode 0 = scatter() returned false, 1 = kDetermined, 2 = kRandom; direction = of the scattered ray;
  *              weight = the factor on the incoming radiance: attenuation, or attenuation * p_scattered / pdf_value */
 int b200rt_scatter(b200rt_ctx *ctx, const double *rays7, const double *rec12, const double *draws6, size_t n, double *out16);
+
+/* ------------------------------------------------------------------ several GPUs of one box
+ * Replaces: the parallel row loop of camera::render (src/camera.h:158) at the scale of a box: the frame is split by SAMPLE
+ * RANGE across the devices of a group (samples are independent, src/camera.h:163-170; the scene is replicated), device g of G
+ * renders the global sample indices [begin + g*span/G, ...) of every pixel, and the fp64 accumulators are summed onto the
+ * first device with one NCCL reduce over NVLink (ncclCommInitAll: single process, one communicator per device) - or by a
+ * peer-access kernel.  Philox draws are keyed by the global sample index, so the set of samples - and, up to fp64 summation
+ * order, the image - does not depend on the number of devices.  One host thread per device inside every call. */
+typedef struct b200rt_group b200rt_group;
+#define B200RT_GROUP_OPT_REDUCE 1000 /* b200rt_group_set_option: how the accumulators are combined */
+#define B200RT_GROUP_REDUCE_NCCL 0   /* ncclReduce(sum, root = first device) (default) */
+#define B200RT_GROUP_REDUCE_PEER 1   /* one kernel on the first device adds the others' buffers through peer (NVLink) loads, in device order */
+int b200rt_group_create(const int *devices, int n, b200rt_group **out);
+int b200rt_group_destroy(b200rt_group *group);
+int b200rt_group_size(const b200rt_group *group);
+/* The context of member i (borrowed; member 0 holds the combined image and serves b200rt_finalize / b200rt_format_ppm). */
+int b200rt_group_context(b200rt_group *group, int i, b200rt_ctx **out);
+/* Any b200rt_option (applied to every member) or B200RT_GROUP_OPT_REDUCE. */
+int b200rt_group_set_option(b200rt_group *group, int option, double value);
+int b200rt_group_upload_scene(b200rt_group *group, const b200rt_scene_desc *scene);
+int b200rt_group_set_camera(b200rt_group *group, const b200rt_camera *camera);
+/* b200rt_render over the whole group: rgb_sum (host, W*H*3) receives the sum over samples [spp_begin, spp_end).
+ * stats: samples / rays / launches summed over the devices, gpu_ms = the slowest device. */
+int b200rt_group_render(b200rt_group *group, uint64_t seed, int spp_begin, int spp_end, double *rgb_sum, b200rt_stats *stats);
+const char *b200rt_group_reduce_backend(void); /* e.g. "NCCL 2.27.3 (dlopen)" once a group of more than one device exists */
 
 /* sizeof() of the ABI structures as compiled into the library (0 scene_desc, 1 camera, 2 stats, 3 node, 4 material,
  * 5 texture, 6 image, 7 volume, 8 value_noise, 9 bvh_info): lets foreign-language bindings check their mirrors. */

@@ -67,18 +67,58 @@
 #undef private
 
 // The adaptor's b200::render (the drop-in for camera::render) is compiled here too, so that the test suite can drive the
-// whole reference-side binding: reference objects -> adaptor -> C ABI -> GPU -> P3 file.  Its b200rt_* calls are weak: this
-// checker library must load (and serve the oracle tests) where libb200rt.so is not loaded; ref_render_b200 reports that.
+// whole reference-side binding: reference objects -> adaptor -> C ABI -> GPU -> P3 file.  This checker library must load
+// (and serve the oracle tests and the CPU reference arm of bench.py) WITHOUT the product library in the process, so the
+// adaptor's b200rt_* calls go through function pointers that ref_render_b200 fills with dlopen / dlsym when it is called.
 #include "b200rt.h"
-#pragma weak b200rt_create
-#pragma weak b200rt_destroy
-#pragma weak b200rt_last_error
-#pragma weak b200rt_upload_scene
-#pragma weak b200rt_set_camera
-#pragma weak b200rt_render
-#pragma weak b200rt_finalize
-#pragma weak b200rt_ppm_bound
-#pragma weak b200rt_format_ppm
+namespace b200dyn {
+#define B200DYN(name) decltype(&::name) name = nullptr;
+B200DYN(b200rt_create)
+B200DYN(b200rt_destroy)
+B200DYN(b200rt_last_error)
+B200DYN(b200rt_upload_scene)
+B200DYN(b200rt_set_camera)
+B200DYN(b200rt_render)
+B200DYN(b200rt_finalize)
+B200DYN(b200rt_ppm_bound)
+B200DYN(b200rt_format_ppm)
+#undef B200DYN
+void *handle = nullptr;
+bool bind(const char *path, std::string &err) {
+  if (handle) return true;
+  handle = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+  if (!handle) {
+    err = std::string("dlopen ") + path + ": " + dlerror();
+    return false;
+  }
+#define B200DYN(name)                                                                                                  \
+  name = (decltype(name))dlsym(handle, #name);                                                                          \
+  if (!name) {                                                                                                         \
+    err = "libb200rt.so does not export " #name;                                                                       \
+    return false;                                                                                                      \
+  }
+  B200DYN(b200rt_create)
+  B200DYN(b200rt_destroy)
+  B200DYN(b200rt_last_error)
+  B200DYN(b200rt_upload_scene)
+  B200DYN(b200rt_set_camera)
+  B200DYN(b200rt_render)
+  B200DYN(b200rt_finalize)
+  B200DYN(b200rt_ppm_bound)
+  B200DYN(b200rt_format_ppm)
+#undef B200DYN
+  return true;
+}
+} // namespace b200dyn
+#define b200rt_create (*b200dyn::b200rt_create)
+#define b200rt_destroy (*b200dyn::b200rt_destroy)
+#define b200rt_last_error (*b200dyn::b200rt_last_error)
+#define b200rt_upload_scene (*b200dyn::b200rt_upload_scene)
+#define b200rt_set_camera (*b200dyn::b200rt_set_camera)
+#define b200rt_render (*b200dyn::b200rt_render)
+#define b200rt_finalize (*b200dyn::b200rt_finalize)
+#define b200rt_ppm_bound (*b200dyn::b200rt_ppm_bound)
+#define b200rt_format_ppm (*b200dyn::b200rt_format_ppm)
 #include "b200rt_adaptor.hpp"
 
 // ------------------------------------------------------------------------------------------------
@@ -966,14 +1006,11 @@ size_t ref_write_colors(const double *rgb, int W, int H, char *out, size_t cap) 
 }
 
 // b200::render(cam, out, world, light) — the binding of INTEGRATION.md — in place of cam.render(out, world, light).
-// Needs libb200rt.so loaded with RTLD_GLOBAL before this library.  Returns wall seconds, < 0 on error (ref_last_error()).
-double ref_render_b200(int h, unsigned long long seed, int spp, int device, const char *ppm_path, double *rgb_linear) {
+// `product_lib` = path of libb200rt.so, loaded here on first use.  Returns wall seconds, < 0 on error (ref_last_error()).
+double ref_render_b200(int h, unsigned long long seed, int spp, int device, const char *ppm_path, double *rgb_linear, const char *product_lib) {
   scene *s = get(h);
   if (!s) return -1.0;
-  if (!b200rt_create || !b200rt_format_ppm) {
-    t_err = "libb200rt.so is not loaded (load it with RTLD_GLOBAL first)";
-    return -2.0;
-  }
+  if (!product_lib || !b200dyn::bind(product_lib, t_err)) return -2.0;
   camera &cam = s->cam;
   int keep = cam.samples_per_pixel_;
   if (spp > 0) cam.samples_per_pixel_ = spp;

@@ -46,11 +46,8 @@ def lib():
     if _lib is None:
         if not available():
             raise RuntimeError(f"{LIB_PATH} missing: run `make -f oracle/Makefile ref` where /root/reference exists")
-        # the harness also compiles the reference-side binding (b200::render of include/b200rt_adaptor.hpp); its b200rt_*
-        # calls are weak and resolve only if the product library is already loaded globally
-        product = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "cpu-ray-tracing-implementation_b200", "libb200rt.so")
-        if os.path.exists(product):
-            C.CDLL(product, mode=C.RTLD_GLOBAL)
+        # the harness also compiles the reference-side binding (b200::render of include/b200rt_adaptor.hpp); the product
+        # library is loaded by ref_render_b200 itself, only when that entry is called (never by the CPU reference arm)
         L = C.CDLL(LIB_PATH)
         vp, u32, i32, sz, dbl = C.c_void_p, C.c_uint, C.c_int, C.c_size_t, C.c_double
         L.ref_last_error.restype = C.c_char_p
@@ -68,7 +65,7 @@ def lib():
         L.ref_render_stock.argtypes = [i32, u32, i32, C.c_char_p, vp]
         L.ref_render_stock.restype = dbl
         L.ref_pstl_is_parallel.restype = i32
-        L.ref_render_b200.argtypes = [i32, C.c_uint64, i32, i32, C.c_char_p, vp]
+        L.ref_render_b200.argtypes = [i32, C.c_uint64, i32, i32, C.c_char_p, vp, C.c_char_p]
         L.ref_render_b200.restype = dbl
         _lib = L
     return _lib
@@ -165,7 +162,8 @@ class RefScene:
 def _render_b200(self, spp=0, seed=0x5EED, device=0, ppm_path=None):
     """b200::render(cam, out, world, light): the drop-in binding in place of camera::render. -> (seconds, linear image)"""
     img = np.zeros(self.npix * 3, np.float64)
-    secs = lib().ref_render_b200(self.h, seed, spp, device, ppm_path.encode() if ppm_path else None, img.ctypes.data)
+    product = os.path.join(_ROOT, "cpu-ray-tracing-implementation_b200", "libb200rt.so")
+    secs = lib().ref_render_b200(self.h, seed, spp, device, ppm_path.encode() if ppm_path else None, img.ctypes.data, product.encode())
     if secs < 0:
         raise RuntimeError("ref_render_b200: " + lib().ref_last_error().decode())
     return secs, img.reshape(self.camera.image_height, self.camera.image_width, 3)

