@@ -25,6 +25,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+OUT = sys.stdout  # replaced in __main__: the descriptor the single JSON line is written to
 
 UNIT = "Mrays/s"
 METRIC = "Mrays/s on RTOW final scene (1200x675, 500 spp, depth 50); Msamples/s alongside; other configs under per_scene"
@@ -165,7 +166,7 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": th, "kind": kind,
                              "sample": f"{args.steps} steps x {spp_step} spp of the 1200x675 frame, {th} threads, wall {wall:.1f} s"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line))
+    print(json.dumps(line), file=OUT, flush=True)
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -379,10 +380,19 @@ def run_ours(args):
             line["cpu_baseline"] = cpu_baseline(HEADLINE, 12.0)
             for key, d in per_scene.items():
                 d["cpu_baseline"] = cpu_baseline(key, 4.0)
-        print(json.dumps(line))
+        print(json.dumps(line), file=OUT, flush=True)
     arm.ctx.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def main_stdout_only_json():
+    """Libraries write to stdout too (NCCL prints its version line there): fd 1 is pointed at stderr for the whole run and the
+    JSON line goes to the real stdout, so that stdout carries exactly ONE line."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(real, "w")
 
 
 if __name__ == "__main__":
@@ -407,6 +417,7 @@ if __name__ == "__main__":
     ap.add_argument("--weak", action="store_true", help="weak scaling instead: every rank renders the config's full spp (secondary figure)")
     ap.add_argument("--no-scenes", action="store_true", help="skip the per_scene measurements (C1, C3, C4, C5 slice)")
     a = ap.parse_args()
+    OUT = main_stdout_only_json()
     if a.impl == "reference":
         run_reference(a)
     else:

@@ -13,10 +13,10 @@ ABI_VERSION = 1
 NODE_BVH, NODE_LIST, NODE_TRANSLATE, NODE_ROTATE_X, NODE_ROTATE_Y, NODE_ROTATE_Z = 0, 1, 2, 3, 4, 5
 NODE_SPHERE, NODE_QUAD, NODE_TRIANGLE, NODE_VOLUME = 6, 7, 8, 9
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_GLOSS, MAT_ISOTROPIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3, 4, 5
-TEX_SOLID, TEX_CHECKER, TEX_PICTURE, TEX_PERLIN, TEX_VALUE, TEX_WORLEY, TEX_VORONOI = 0, 1, 2, 3, 4, 5, 6
+TEX_SOLID, TEX_CHECKER, TEX_PICTURE, TEX_PERLIN, TEX_VALUE, TEX_WORLEY, TEX_VORONOI, TEX_PICTURE_LINEAR = 0, 1, 2, 3, 4, 5, 6, 7
 LIGHT_NONE, LIGHT_QUAD, LIGHT_SPHERE, LIGHT_DEFAULT = 0, 1, 2, 3
 CAM_PERSPECTIVE, CAM_ORTHOGRAPHIC, CAM_FISHEYE, CAM_LENS = 0, 1, 2, 3
-OPT_TRAVERSAL, OPT_WAVE_PATHS, OPT_KILL_ZERO_WEIGHT, OPT_BVH_LEAF_SIZE, OPT_RESERVED_4, OPT_REFILL_LANES, OPT_EXTEND_BLOCKS, OPT_SPECULATIVE_LEAF, OPT_FUSE_MISS, OPT_EXTEND_STAGES, OPT_SMEM_CARVEOUT, OPT_BVH_BUILDER, OPT_BVH_WIDTH, OPT_PIPELINES, OPT_PIPE_EXTEND_CTAS, OPT_TAIL_PATHS, OPT_WAVE_LOOP = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16
+OPT_TRAVERSAL, OPT_WAVE_PATHS, OPT_KILL_ZERO_WEIGHT, OPT_BVH_LEAF_SIZE, OPT_RESERVED_4, OPT_REFILL_LANES, OPT_EXTEND_BLOCKS, OPT_SPECULATIVE_LEAF, OPT_FUSE_MISS, OPT_EXTEND_STAGES, OPT_SMEM_CARVEOUT, OPT_BVH_BUILDER, OPT_BVH_WIDTH, OPT_PIPELINES, OPT_PIPE_EXTEND_CTAS, OPT_TAIL_PATHS, OPT_WAVE_LOOP, OPT_EXTEND_LOOP, OPT_LEAF_LANES, OPT_L2_PERSIST, OPT_TRI_F32 = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20
 BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1
 TRAVERSAL_FAST, TRAVERSAL_MIRROR = 0, 1
 
@@ -164,6 +164,8 @@ EXPORTS = [
     "b200rt_texture_sample",
     "b200rt_scatter",
     "b200rt_abi_sizeof",
+    "b200rt_image_bound",
+    "b200rt_format_image",
     "b200rt_group_create",
     "b200rt_group_destroy",
     "b200rt_group_size",
@@ -175,6 +177,7 @@ EXPORTS = [
     "b200rt_group_reduce_backend",
 ]
 GROUP_OPT_REDUCE, GROUP_REDUCE_NCCL, GROUP_REDUCE_PEER = 1000, 0, 1
+IMAGE_PPM_TEXT, IMAGE_PPM_BINARY, IMAGE_EXR = 0, 1, 2
 
 
 def bind(lib):
@@ -199,6 +202,9 @@ def bind(lib):
     lib.b200rt_texture_sample.argtypes = [vp, i32, vp, sz, vp]
     lib.b200rt_scatter.argtypes = [vp, vp, vp, vp, sz, vp]
     lib.b200rt_abi_sizeof.argtypes = [i32]
+    lib.b200rt_image_bound.argtypes = [i32, i32, i32]
+    lib.b200rt_image_bound.restype = C.c_size_t
+    lib.b200rt_format_image.argtypes = [vp, vp, i32, i32, vp, sz, C.POINTER(sz)]
     lib.b200rt_group_create.argtypes = [C.POINTER(i32), i32, C.POINTER(vp)]
     lib.b200rt_group_destroy.argtypes = [vp]
     lib.b200rt_group_size.argtypes = [vp]
@@ -210,7 +216,7 @@ def bind(lib):
     lib.b200rt_group_reduce_backend.argtypes = []
     lib.b200rt_group_reduce_backend.restype = C.c_char_p
     for name in EXPORTS:
-        if name not in ("b200rt_last_error", "b200rt_abi_sizeof", "b200rt_ppm_bound", "b200rt_group_reduce_backend"):
+        if name not in ("b200rt_last_error", "b200rt_abi_sizeof", "b200rt_ppm_bound", "b200rt_group_reduce_backend", "b200rt_image_bound"):
             getattr(lib, name).restype = C.c_int
     lib.b200rt_abi_sizeof.restype = C.c_size_t
     lib.b200rt_ppm_bound.restype = C.c_size_t

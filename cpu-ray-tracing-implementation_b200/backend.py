@@ -11,7 +11,7 @@ import numpy as np
 from . import _abi as abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200rt.so")
+LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(_HERE, "libb200rt.so")  # B200RT_LIB: another build of the SAME library (A/B experiments)
 
 
 class B200RTError(RuntimeError):
@@ -151,6 +151,15 @@ class Context:
         self._check(self._lib.b200rt_format_ppm(self._h, rgb_sum.ctypes.data, total_spp, buf.ctypes.data, cap, C.byref(n)))
         return buf[: n.value].tobytes()
 
+
+    def format_image(self, rgb_sum, total_spp, fmt, capacity=None):
+        """The frame as a complete file image: abi.IMAGE_PPM_TEXT (the reference's P3), IMAGE_PPM_BINARY (P6) or IMAGE_EXR (linear float)."""
+        rgb_sum = np.ascontiguousarray(rgb_sum, dtype=np.float64)
+        cap = int(capacity if capacity is not None else self._lib.b200rt_image_bound(fmt, self.camera.image_width, self.camera.image_height))
+        buf = np.empty(max(cap, 1), np.uint8)
+        n = C.c_size_t(0)
+        self._check(self._lib.b200rt_format_image(self._h, rgb_sum.ctypes.data, total_spp, fmt, buf.ctypes.data, cap, C.byref(n)))
+        return buf[: n.value].tobytes()
 
 
 class Group:

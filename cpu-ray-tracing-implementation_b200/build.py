@@ -26,7 +26,10 @@ def deps():
     return out
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, out=None):
+    global OUT
+    if out:
+        OUT, force = out, True
     if not force and os.path.exists(OUT) and all(os.path.getmtime(OUT) >= os.path.getmtime(d) for d in deps()):
         return OUT
     nvcc = os.environ.get("NVCC", "nvcc")
@@ -42,4 +45,5 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    alt = [a.split("=", 1)[1] for a in sys.argv if a.startswith("--out=")]
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, out=alt[0] if alt else None))

@@ -35,14 +35,32 @@ int fail(int code, const char *fmt, ...) {
 struct DevMem { // owns device allocations of a context
   std::vector<void *> ptrs;
   size_t bytes = 0;
+  // optional arena: one contiguous block that the first allocations are carved from, in call order, so that what the
+  // traversal touches most (BVH nodes, leaf entries, primitive rows) lies in ONE address range that an L2 access-policy
+  // window can cover; what does not fit falls back to cudaMalloc
+  char *arena = nullptr;
+  size_t arena_size = 0, arena_used = 0;
   ~DevMem() { release(); }
   void release() {
     for (void *p : ptrs) cudaFree(p);
     ptrs.clear();
     bytes = 0;
+    arena = nullptr, arena_size = arena_used = 0;
+  }
+  cudaError_t reserve(size_t n) {
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e == cudaSuccess) ptrs.push_back(p), bytes += n, arena = (char *)p, arena_size = n, arena_used = 0;
+    return e;
   }
   cudaError_t alloc(void **p, size_t n) {
     if (n == 0) n = 16;
+    const size_t padded = (n + 255) & ~(size_t)255;
+    if (arena && arena_used + padded <= arena_size) {
+      *p = arena + arena_used;
+      arena_used += padded;
+      return cudaSuccess;
+    }
     cudaError_t e = cudaMalloc(p, n);
     if (e == cudaSuccess) ptrs.push_back(*p), bytes += n;
     return e;
@@ -111,6 +129,12 @@ struct b200rt_ctx {
     }
   } w[B200_MAX_PIPELINES];
   cudaStream_t cap_stream = nullptr; // stream captures are recorded on (never executes anything)
+  int l2_persist = 1;  // B200RT_OPT_L2_PERSIST
+  int tri_f32 = 1;     // B200RT_OPT_TRI_F32
+  size_t hot_bytes = 0; // prefix of the scene arena that the traversal reads per node / leaf
+  size_t l2_window_max = 0, l2_persist_max = 0;
+  int extend_loop = 0; // B200RT_OPT_EXTEND_LOOP: 0 = while-while, 1 = warp-uniform threshold if-if
+  int leaf_lanes = 8;  // B200RT_OPT_LEAF_LANES
   int wave_loop = 1; // B200RT_OPT_WAVE_LOOP: 1 = device-driven CUDA-graph while loop, 0 = host-driven loop with read-backs
   cudaEvent_t ev_fork = nullptr;
   int pipelines = 2;        // measured: +4 % on RTOW, +5 % on the Sponza stand-in over one pipeline (profiles/r01_r_pipelines.txt)
@@ -230,14 +254,15 @@ int validate(const b200rt_scene_desc *d) {
   }
   for (uint32_t i = 0; i < d->n_textures; i++) {
     const b200rt_texture &t = d->textures[i];
-    if (t.kind < 0 || t.kind > B200RT_TEX_VORONOI) return fail(B200RT_ERR_UNSUPPORTED, "texture %u: unknown kind %d", i, t.kind);
-    if (t.kind == B200RT_TEX_PICTURE && (t.aux < 0 || (uint32_t)t.aux >= d->n_images)) return fail(B200RT_ERR_INVALID, "texture %u: image out of range", i);
+    if (t.kind < 0 || t.kind > B200RT_TEX_PICTURE_LINEAR) return fail(B200RT_ERR_UNSUPPORTED, "texture %u: unknown kind %d", i, t.kind);
+    if ((t.kind == B200RT_TEX_PICTURE || t.kind == B200RT_TEX_PICTURE_LINEAR) && (t.aux < 0 || (uint32_t)t.aux >= d->n_images)) return fail(B200RT_ERR_INVALID, "texture %u: image out of range", i);
     if (t.kind == B200RT_TEX_PERLIN && (t.aux < 0 || (uint32_t)t.aux >= d->n_perlin)) return fail(B200RT_ERR_INVALID, "texture %u: perlin table out of range", i);
     if (t.kind == B200RT_TEX_VALUE && (t.aux < 0 || (uint32_t)t.aux >= d->n_value_noise)) return fail(B200RT_ERR_INVALID, "texture %u: value-noise table out of range", i);
   }
   for (uint32_t i = 0; i < d->n_images; i++) {
     const b200rt_image &im = d->images[i];
-    if (im.has_data && (im.width <= 0 || im.height <= 0 || (im.bytes_per_pixel != 3 && im.bytes_per_pixel != 4) ||
+    if (im.has_data && (im.width <= 0 || im.height <= 0 || (im.bytes_per_pixel != 3 && im.bytes_per_pixel != 4 && im.bytes_per_pixel != 12 && im.bytes_per_pixel != 16) ||
+                        (im.bytes_per_pixel >= 12 && im.offset % 4 != 0) ||
                         im.offset + (uint64_t)im.width * im.height * im.bytes_per_pixel > d->image_bytes_size))
       return fail(B200RT_ERR_INVALID, "image %u: bad geometry or bytes out of range", i);
   }
@@ -286,6 +311,8 @@ int b200rt_create(int device, b200rt_ctx **out) {
   std::unique_ptr<b200rt_ctx> c(new b200rt_ctx);
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
+  c->l2_window_max = (size_t)std::max(0, prop.accessPolicyMaxWindowSize);
+  c->l2_persist_max = (size_t)std::max(0, prop.persistingL2CacheMaxSize);
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(cudaEventCreate(&c->ev0));
   CU(cudaEventCreate(&c->ev1));
@@ -370,6 +397,16 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     if (!(value >= -1 && value <= 100)) return fail(B200RT_ERR_INVALID, "carve-out must be -1 (automatic) or a percentage");
     c->carveout_pct = (int)value;
     return B200RT_OK;
+  case B200RT_OPT_L2_PERSIST: c->l2_persist = value != 0; return B200RT_OK;
+  case B200RT_OPT_TRI_F32: c->tri_f32 = value != 0; return B200RT_OK; // takes effect at the next b200rt_upload_scene
+  case B200RT_OPT_EXTEND_LOOP:
+    if (value != 0 && value != 1) return fail(B200RT_ERR_INVALID, "extend loop must be 0 (while-while) or 1 (warp-uniform)");
+    c->extend_loop = (int)value;
+    return B200RT_OK;
+  case B200RT_OPT_LEAF_LANES:
+    if (!(value >= 1 && value <= 32)) return fail(B200RT_ERR_INVALID, "leaf lanes must be in [1, 32]");
+    c->leaf_lanes = (int)value;
+    return B200RT_OK;
   case B200RT_OPT_WAVE_LOOP:
     if (value != 0 && value != 1) return fail(B200RT_ERR_INVALID, "wave loop must be 0 (host-driven) or 1 (device-driven CUDA graph)");
     c->wave_loop = (int)value;
@@ -429,17 +466,87 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   DevScene S;
   std::memset(&S, 0, sizeof S);
   S.root = d->root;
-  UP(d->nodes, d->n_nodes, &S.nodes, "nodes");
-  UP(d->list_children, d->n_list_children, &S.list_children, "list_children");
+  // the tree that is traversed: the BVH2, or the BVH4 collapsed from it
+  std::vector<BvhNode4> wide;
+  if (!use_device_builder) {
+    const int width = c->bvh_width ? c->bvh_width : (ordered.size() > B200_WIDE_FROM_PRIMS ? 4 : 2);
+    if (width == 4 && bvh.root >= 0) {
+      int32_t root4 = B200_EMPTY_ROOT;
+      uint32_t depth4 = 0;
+      wide = collapse4(bvh, root4, depth4);
+      if (3 * depth4 <= B200_STACK) { // up to three pushes per level; deeper trees keep the BVH2
+        bvh.root = root4;
+        n_nodes4 = (uint32_t)wide.size();
+        bvh.max_depth = depth4;
+      } else {
+        wide.clear();
+      }
+    }
+  }
+  // triangle vertices as binary32 rows when every coordinate is exactly representable (glTF positions are: src/main.cc:361-365):
+  // 48 bytes per triangle test instead of 80, widened after the load, so the binary64 arithmetic sees identical operands
+  std::vector<float> tri32;
+  if (c->tri_f32 && d->n_tris) {
+    tri32.resize((size_t)d->n_tris * 12, 0.0f);
+    bool exact = true;
+    for (size_t i = 0; i < d->n_tris && exact; i++)
+      for (int k = 0; k < 9; k++) {
+        const double v = d->tris[i * B200RT_TRI_STRIDE + k];
+        const float f = (float)v;
+        if (!((double)f == v)) { // also rejects NaN
+          exact = false;
+          break;
+        }
+        tri32[i * 12 + k] = f;
+      }
+    if (!exact) tri32.clear();
+  }
+  {
+    auto pad = [](size_t n) { return ((n ? n : 16) + 255) & ~(size_t)255; };
+    size_t total = 0;
+    total += pad(wide.size() * sizeof(BvhNode4)) + pad(bvh.nodes.size() * sizeof(BvhNode)) + pad(ordered.size() * sizeof(Entry)) + pad(ordered.size());
+    total += pad(tri32.size() * 4) + pad((size_t)d->n_tris * B200RT_TRI_STRIDE * 8) + pad((size_t)d->n_spheres * B200RT_SPHERE_STRIDE * 8) + pad((size_t)d->n_quads * B200RT_QUAD_STRIDE * 8);
+    total += pad(fs.chain_ops.size() * sizeof(ChainOp)) + pad(fs.chains.size() * sizeof(Chain)) + pad(fs.vol_inst.size() * sizeof(VolInst)) + pad(fs.bentries.size() * sizeof(Entry));
+    total += pad((size_t)d->n_spheres * 4) + pad((size_t)d->n_quads * 4) + pad((size_t)d->n_tris * 4) + pad(d->n_volumes * sizeof(b200rt_volume));
+    total += pad(d->n_materials * sizeof(b200rt_material)) + pad(d->n_textures * sizeof(b200rt_texture));
+    CU(c->scene_mem.reserve(total)); // images, noise tables and the reference graph (mirror traversal only) stay outside
+  }
+  // ---- hot: read per node / per leaf by the traversal
+  if (!use_device_builder) {
+    if (!wide.empty())
+      UP(wide.data(), wide.size(), &S.bvh4, "bvh4");
+    else
+      UP(bvh.nodes.data(), bvh.nodes.size(), &S.bvh, "bvh");
+    UP(ordered.data(), ordered.size(), &S.entries, "entries");
+  }
+  if (!tri32.empty()) {
+    const float *p32 = nullptr;
+    UP(tri32.data(), tri32.size(), &p32, "tri32");
+    S.tri32 = reinterpret_cast<const float4 *>(p32);
+  }
   UP(d->spheres, (size_t)d->n_spheres * B200RT_SPHERE_STRIDE, &S.spheres, "spheres");
-  UP(d->sphere_mat, d->n_spheres, &S.sphere_mat, "sphere_mat");
   UP(d->quads, (size_t)d->n_quads * B200RT_QUAD_STRIDE, &S.quads, "quads");
+  if (tri32.empty()) UP(d->tris, (size_t)d->n_tris * B200RT_TRI_STRIDE, &S.tris, "tris");
+  UP(fs.chain_ops.data(), fs.chain_ops.size(), &S.chain_ops, "chain_ops");
+  UP(fs.chains.data(), fs.chains.size(), &S.chains, "chains");
+  c->hot_bytes = c->scene_mem.arena_used;
+  if (c->l2_persist && c->l2_persist_max) { // L2 set-aside for the persisting window (device-wide limit; rounded by the driver)
+    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min(c->l2_persist_max, (c->hot_bytes + ((size_t)1 << 20)) & ~(((size_t)1 << 20) - 1)));
+    cudaGetLastError();
+  }
+  // ---- warm: read per finished ray / per shaded hit
+  if (!tri32.empty()) UP(d->tris, (size_t)d->n_tris * B200RT_TRI_STRIDE, &S.tris, "tris"); // normals for finish_hit
+  UP(d->sphere_mat, d->n_spheres, &S.sphere_mat, "sphere_mat");
   UP(d->quad_mat, d->n_quads, &S.quad_mat, "quad_mat");
-  UP(d->tris, (size_t)d->n_tris * B200RT_TRI_STRIDE, &S.tris, "tris");
   UP(d->tri_mat, d->n_tris, &S.tri_mat, "tri_mat");
   UP(d->volumes, d->n_volumes, &S.volumes, "volumes");
   UP(d->materials, d->n_materials, &S.materials, "materials");
   UP(d->textures, d->n_textures, &S.textures, "textures");
+  UP(fs.vol_inst.data(), fs.vol_inst.size(), &S.vol_inst, "vol_inst");
+  UP(fs.bentries.data(), fs.bentries.size(), &S.bentries, "bentries");
+  // ---- cold
+  UP(d->nodes, d->n_nodes, &S.nodes, "nodes");
+  UP(d->list_children, d->n_list_children, &S.list_children, "list_children");
   UP(d->images, d->n_images, &S.images, "images");
   UP(d->image_bytes, d->image_bytes_size, &S.image_bytes, "image_bytes");
   UP(d->perlin_vec, (size_t)d->n_perlin * 768, &S.perlin_vec, "perlin_vec");
@@ -452,26 +559,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   if (use_device_builder) {
     rc = build_bvh_device(c, fs, S, c->bvh_info);
     if (rc != B200RT_OK) return rc;
-  } else {
-    UP(bvh.nodes.data(), bvh.nodes.size(), &S.bvh, "bvh");
-    UP(ordered.data(), ordered.size(), &S.entries, "entries");
-    const int width = c->bvh_width ? c->bvh_width : (ordered.size() > B200_WIDE_FROM_PRIMS ? 4 : 2);
-    if (width == 4 && bvh.root >= 0) {
-      int32_t root4 = B200_EMPTY_ROOT;
-      uint32_t depth4 = 0;
-      const std::vector<BvhNode4> wide = collapse4(bvh, root4, depth4);
-      if (3 * depth4 <= B200_STACK) { // up to three pushes per level; deeper trees keep the BVH2
-        UP(wide.data(), wide.size(), &S.bvh4, "bvh4");
-        bvh.root = root4;
-        n_nodes4 = (uint32_t)wide.size();
-        bvh.max_depth = depth4;
-      }
-    }
   }
-  UP(fs.bentries.data(), fs.bentries.size(), &S.bentries, "bentries");
-  UP(fs.vol_inst.data(), fs.vol_inst.size(), &S.vol_inst, "vol_inst");
-  UP(fs.chain_ops.data(), fs.chain_ops.size(), &S.chain_ops, "chain_ops");
-  UP(fs.chains.data(), fs.chains.size(), &S.chains, "chains");
   if (!use_device_builder) {
     S.bvh_root = bvh.root;
     S.n_bvh_nodes = (uint32_t)bvh.nodes.size();
@@ -479,6 +567,13 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
     for (int k = 0; k < 3; k++) S.bound[k] = bvh.bound[k];
   }
   S.has_volumes = fs.has_volumes ? 1 : 0;
+  { // per entry: the shade queue of its material, derived on the device from what has just been uploaded
+    uint8_t *eq = nullptr;
+    CU(c->scene_mem.alloc((void **)&eq, S.n_entries));
+    if (S.n_entries) k_fill_entry_queue<<<(int)((S.n_entries + 255) / 256), 256, 0, c->stream>>>(S, eq);
+    CU(cudaGetLastError());
+    S.entry_queue = eq;
+  }
   CU(cudaStreamSynchronize(c->stream)); // host vectors go out of scope
   c->S = S;
   if (!use_device_builder) {
@@ -751,7 +846,11 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, const Dev
     case 9: EXT(128, true, 4, 2); break;
 #undef EXT
     default: // 128 registers, 4-warp CTAs
-      if (c->S.bvh4)
+      if (c->extend_loop == 1 && c->S.bvh4)
+        launch_extend(k_extend_persistent<128, false, 4, 2, true, true>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);
+      else if (c->extend_loop == 1)
+        launch_extend(k_extend_persistent<128, false, 4, 2, false, true>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);
+      else if (c->S.bvh4)
         launch_extend(k_extend_persistent<128, false, 4, 2, true>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);
       else if (c->extend_stages == 1 && wp.refill == 32)
         launch_extend(k_extend_persistent<128, false, 4, 1, false>, c, w, ext_ctas, 128, 4 * 1 * 3584, s, cur, wp);
@@ -767,6 +866,26 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, const Dev
   else
     k_ctl_swap<<<1, 1, 0, s>>>(w.ctl);
   return (mirror ? 2 : 3) + (tail ? 1 : 0) + n_gen_launches + n_shade;
+}
+
+// The hot prefix of the scene arena (tree, leaf entries, primitive rows) as a persisting L2 window: what every ray re-reads
+// stays in L2 while the wave's path state streams through it.  Returns false when the device / scene has nothing to pin.
+bool l2_window(const b200rt_ctx *c, cudaAccessPolicyWindow &w) {
+  if (!c->l2_persist || !c->hot_bytes || !c->l2_window_max || !c->l2_persist_max || !c->scene_mem.arena) return false;
+  const size_t win = std::min(c->hot_bytes, c->l2_window_max);
+  w.base_ptr = c->scene_mem.arena;
+  w.num_bytes = win;
+  w.hitRatio = (float)std::min(1.0, (double)c->l2_persist_max / (double)win);
+  w.hitProp = cudaAccessPropertyPersisting;
+  w.missProp = cudaAccessPropertyStreaming;
+  return true;
+}
+void l2_window_on_stream(const b200rt_ctx *c, cudaStream_t s) {
+  cudaStreamAttrValue v;
+  std::memset(&v, 0, sizeof v);
+  if (!l2_window(c, v.accessPolicyWindow)) v.accessPolicyWindow.num_bytes = 0; // a zero-size window switches the policy off
+  cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &v);
+  cudaGetLastError(); // a refused hint is not an error of the render
 }
 
 // The device-driven wave loop of one pipeline as a CUDA graph: a single conditional WHILE node whose body is one wave
@@ -787,6 +906,7 @@ int ensure_wave_graph(b200rt_ctx *c, b200rt_ctx::WaveSet &w, const std::string &
   cudaGraphNode_t node;
   CU(cudaGraphAddNode(&node, w.graph, nullptr, 0, &np));
   cudaGraph_t body = np.conditional.phGraph_out[0];
+  l2_window_on_stream(c, c->cap_stream);
   CU(cudaStreamBeginCaptureToGraph(c->cap_stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
   const int n = launch_wave(c, w, c->cap_stream, cam, wp, g_gen, g_ext, d_rgb_sum, ext_ctas, nullptr, more);
   cudaGraph_t captured = nullptr;
@@ -798,6 +918,22 @@ int ensure_wave_graph(b200rt_ctx *c, b200rt_ctx::WaveSet &w, const std::string &
   if (e_end != cudaSuccess) {
     w.drop_graph();
     return fail(B200RT_ERR_CUDA, "capturing the wave graph: %s", cudaGetErrorString(e_end));
+  }
+  { // the access-policy window on every kernel node of the body (explicitly: not every driver carries the capturing stream's over)
+    cudaLaunchAttributeValue av;
+    std::memset(&av, 0, sizeof av);
+    if (l2_window(c, av.accessPolicyWindow)) {
+      size_t n_nodes = 0;
+      if (cudaGraphGetNodes(body, nullptr, &n_nodes) == cudaSuccess && n_nodes) {
+        std::vector<cudaGraphNode_t> nodes(n_nodes);
+        cudaGraphGetNodes(body, nodes.data(), &n_nodes);
+        for (cudaGraphNode_t nd : nodes) {
+          cudaGraphNodeType ty;
+          if (cudaGraphNodeGetType(nd, &ty) == cudaSuccess && ty == cudaGraphNodeTypeKernel) cudaGraphKernelNodeSetAttribute(nd, cudaLaunchAttributeAccessPolicyWindow, &av);
+        }
+      }
+      cudaGetLastError();
+    }
   }
   const cudaError_t e_inst = cudaGraphInstantiate(&w.graph_exec, w.graph, 0);
   if (e_inst != cudaSuccess) {
@@ -854,6 +990,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     q.max_depth = c->cam.max_depth;
     q.kill_zero = c->kill_zero;
     q.fused_miss = (mirror || !c->fuse_miss) ? 0 : c->bg_mode;
+    q.leaf_lanes = c->leaf_lanes;
     q.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 8 : 32);
     for (int k = 0; k < 3; k++) q.bound[k] = c->S.bound[k];
     tot[p] = (unsigned long long)npix * (unsigned long long)(hi - lo);
@@ -876,6 +1013,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   }
 
   const bool use_graph = c->wave_loop == 1 && !mirror;
+  for (int p = 0; p < n_pipe; p++) l2_window_on_stream(c, ps[p]);
   // Whatever happens below (a failed launch, a failed copy), the forked pipeline streams are joined back into the caller's
   // stream and the per-launch timing events are destroyed: the caller may keep using `s` and d_rgb_sum after an error.
   struct WaveLoopGuard {
@@ -917,7 +1055,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     for (int p = 0; p < n_pipe; p++) {
       std::string key;
       key_add(key, c->S), key_add(key, cam), key_add(key, wp[p]), key_add(key, cap[p]), key_add(key, d_rgb_sum), key_add(key, ext_ctas);
-      key_add(key, c->tail_paths), key_add(key, c->extend_blocks), key_add(key, c->speculative), key_add(key, c->extend_stages), key_add(key, c->carveout_pct);
+      key_add(key, c->tail_paths), key_add(key, c->extend_blocks), key_add(key, c->speculative), key_add(key, c->extend_stages), key_add(key, c->carveout_pct), key_add(key, c->extend_loop), key_add(key, c->l2_persist);
       key_add(key, c->kinds_present), key_add(key, c->w[p].pools), key_add(key, c->w[p].hits);
       if ((rc = ensure_wave_graph(c, c->w[p], key, cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas)) != B200RT_OK) return rc;
       CU(cudaGraphLaunch(c->w[p].graph_exec, ps[p]));
@@ -1072,6 +1210,108 @@ int b200rt_format_ppm(b200rt_ctx *c, const double *rgb_sum, int total_spp, char 
   CU(cudaMemcpyAsync(out + hl, d_out + hl, (size_t)total - hl, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   std::memcpy(out, header, hl);
+  return B200RT_OK;
+}
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------------------------ binary image writers
+namespace {
+void exr_attr(std::string &h, const char *name, const char *type, const void *data, int32_t size) {
+  h.append(name).push_back('\0');
+  h.append(type).push_back('\0');
+  h.append(reinterpret_cast<const char *>(&size), 4);
+  h.append(reinterpret_cast<const char *>(data), (size_t)size);
+}
+// magic, version, attributes, terminator; padded (with a trailing comment attribute) so that header + offset table end on a multiple of 4
+std::string exr_header(int W, int H) {
+  std::string h;
+  const unsigned char magic[8] = {0x76, 0x2f, 0x31, 0x01, 2, 0, 0, 0};
+  h.append(reinterpret_cast<const char *>(magic), 8);
+  std::string ch;
+  for (const char *nm : {"B", "G", "R"}) {
+    ch.append(nm).push_back('\0');
+    const int32_t type = 2 /* FLOAT */, samp = 1;
+    const unsigned char lin[4] = {0, 0, 0, 0};
+    ch.append(reinterpret_cast<const char *>(&type), 4);
+    ch.append(reinterpret_cast<const char *>(lin), 4);
+    ch.append(reinterpret_cast<const char *>(&samp), 4);
+    ch.append(reinterpret_cast<const char *>(&samp), 4);
+  }
+  ch.push_back('\0');
+  exr_attr(h, "channels", "chlist", ch.data(), (int32_t)ch.size());
+  const unsigned char none = 0;
+  exr_attr(h, "compression", "compression", &none, 1);
+  const int32_t win[4] = {0, 0, W - 1, H - 1};
+  exr_attr(h, "dataWindow", "box2i", win, 16);
+  exr_attr(h, "displayWindow", "box2i", win, 16);
+  exr_attr(h, "lineOrder", "lineOrder", &none, 1);
+  const float one = 1.0f, zero2[2] = {0.0f, 0.0f};
+  exr_attr(h, "pixelAspectRatio", "float", &one, 4);
+  exr_attr(h, "screenWindowCenter", "v2f", zero2, 8);
+  exr_attr(h, "screenWindowWidth", "float", &one, 4);
+  const std::string base = "b200rt linear radiance (pixel_color / samples_per_pixel), no gamma";
+  // "comments" string attribute sized so that the scan-line blocks are 4-byte aligned
+  const size_t fixed = h.size() + 9 + 7 + 4 + 1; // name, type, size field, header terminator
+  std::string text = base;
+  while ((fixed + text.size()) % 4 != 0) text.push_back(' ');
+  exr_attr(h, "comments", "string", text.data(), (int32_t)text.size());
+  h.push_back('\0');
+  return h;
+}
+} // namespace
+
+extern "C" {
+
+size_t b200rt_image_bound(int format, int image_width, int image_height) {
+  if (image_width <= 0 || image_height <= 0) return 0;
+  const size_t W = (size_t)image_width, H = (size_t)image_height;
+  switch (format) {
+  case B200RT_IMAGE_PPM_TEXT: return b200rt_ppm_bound(image_width, image_height);
+  case B200RT_IMAGE_PPM_BINARY: return 64 + W * H * 3;
+  case B200RT_IMAGE_EXR: return exr_header(image_width, image_height).size() + 8 * H + H * (8 + 12 * W);
+  }
+  return 0;
+}
+
+int b200rt_format_image(b200rt_ctx *c, const double *rgb_sum, int total_spp, int format, char *out, size_t capacity, size_t *out_len) {
+  if (format == B200RT_IMAGE_PPM_TEXT) return b200rt_format_ppm(c, rgb_sum, total_spp, out, capacity, out_len);
+  if (!c || !rgb_sum || !out || !out_len) return fail(B200RT_ERR_INVALID, "NULL argument");
+  if (!c->have_camera) return fail(B200RT_ERR_STATE, "format_image before b200rt_set_camera");
+  if (total_spp <= 0) return fail(B200RT_ERR_INVALID, "total_spp must be positive");
+  if (format != B200RT_IMAGE_PPM_BINARY && format != B200RT_IMAGE_EXR) return fail(B200RT_ERR_INVALID, "unknown image format %d", format);
+  const int W = c->cam.image_width, H = c->cam.image_height;
+  const size_t npix = (size_t)W * H, need = b200rt_image_bound(format, W, H);
+  std::string head;
+  if (format == B200RT_IMAGE_PPM_BINARY) {
+    char header[64];
+    head.assign(header, (size_t)snprintf(header, sizeof header, "P6\n%d %d\n255\n", W, H));
+  } else {
+    head = exr_header(W, H);
+    const uint64_t first = head.size() + 8ull * (uint64_t)H;
+    for (int y = 0; y < H; y++) {
+      const uint64_t off = first + (uint64_t)y * (8ull + 12ull * (uint64_t)W);
+      head.append(reinterpret_cast<const char *>(&off), 8);
+    }
+  }
+  const size_t payload = format == B200RT_IMAGE_PPM_BINARY ? npix * 3 : (size_t)H * (8 + 12 * (size_t)W);
+  *out_len = head.size() + payload;
+  if (*out_len > capacity) return fail(B200RT_ERR_INVALID, "format_image: the file needs %zu bytes, capacity is %zu (b200rt_image_bound() gives %zu)", *out_len, capacity, need);
+  CU(cudaSetDevice(c->device));
+  DevMem tmp;
+  double *d_sum = nullptr;
+  unsigned char *d_out = nullptr;
+  CU(tmp.alloc((void **)&d_sum, npix * 3 * sizeof(double)));
+  CU(tmp.alloc((void **)&d_out, payload));
+  CU(cudaMemcpyAsync(d_sum, rgb_sum, npix * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  if (format == B200RT_IMAGE_PPM_BINARY)
+    k_pack_p6<<<grid_for(c, npix * 3, 256, 8), 256, 0, c->stream>>>(d_sum, npix * 3, (double)total_spp, d_out);
+  else
+    k_pack_exr<<<grid_for(c, npix, 256, 8), 256, 0, c->stream>>>(d_sum, W, H, (double)total_spp, d_out);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(out + head.size(), d_out, payload, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  std::memcpy(out, head.data(), head.size());
   return B200RT_OK;
 }
 

@@ -169,14 +169,21 @@ DEV bool quad_row_t(const DevScene &S, int row, const Ray &r, double lo, double 
 
 // ---------------------------------------------------------------- triangle
 DEV bool tri_row_t(const DevScene &S, int row, const Ray &r, double lo, double hi, double &t) {
-  const double *q = S.tris + (size_t)row * B200RT_TRI_STRIDE;
-  double a0, a1, a2, b0_, b1_, b2_, c0, c1, c2, nx;
-  ld2(q, a0, a1);
-  ld2(q + 2, a2, b0_);
-  ld2(q + 4, b1_, b2_);
-  ld2(q + 6, c0, c1);
-  ld2(q + 8, c2, nx);
-  const V p0 = v3(a0, a1, a2), p1 = v3(b0_, b1_, b2_), p2 = v3(c0, c1, c2);
+  V p0, p1, p2;
+  if (S.tri32) { // 48-byte binary32 row, widened: the same binary64 operands as the 96-byte row holds (checked at upload)
+    const float4 *q = S.tri32 + (size_t)row * 3;
+    const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+    p0 = v3((double)a.x, (double)a.y, (double)a.z), p1 = v3((double)a.w, (double)b.x, (double)b.y), p2 = v3((double)b.z, (double)b.w, (double)c.x);
+  } else {
+    const double *q = S.tris + (size_t)row * B200RT_TRI_STRIDE;
+    double a0, a1, a2, b0_, b1_, b2_, c0, c1, c2, nx;
+    ld2(q, a0, a1);
+    ld2(q + 2, a2, b0_);
+    ld2(q + 4, b1_, b2_);
+    ld2(q + 6, c0, c1);
+    ld2(q + 8, c2, nx);
+    p0 = v3(a0, a1, a2), p1 = v3(b0_, b1_, b2_), p2 = v3(c0, c1, c2);
+  }
   const V e1 = p1 - p0, e2 = p2 - p0, sv = r.o - p0;
   const V s1 = cross(r.d, e2), s2 = cross(sv, e1);
   const double det = dot(s1, e1);
@@ -206,7 +213,7 @@ DEV bool tri_row_t(const DevScene &S, int row, const Ray &r, double lo, double h
 }
 
 // ---------------------------------------------------------------- volume boundary: closest t over its leaves
-DEV bool boundary_t(const DevScene &S, const VolInst &vi, const Ray &r, double lo, double hi, double &tout) {
+DEV_COLD bool boundary_t(const DevScene &S, const VolInst &vi, const Ray &r, double lo, double hi, double &tout) {
   bool any = false;
   double best = hi;
   for (int k = 0; k < vi.bcount; k++) {
@@ -231,7 +238,7 @@ DEV bool boundary_t(const DevScene &S, const VolInst &vi, const Ray &r, double l
 }
 
 // volumne::hit, src/volumne.h:18-46.  `r` is the ray in the volume's own frame.
-DEV bool volume_t(const DevScene &S, const Entry &e, const Ray &r, double lo, double hi, const Stream &st, int bounce, double &t) {
+DEV_COLD bool volume_t(const DevScene &S, const Entry &e, const Ray &r, double lo, double hi, const Stream &st, int bounce, double &t) {
   const VolInst vi = S.vol_inst[e.row];
   double t1, t2;
   if (!boundary_t(S, vi, r, -B200_INF, B200_INF, t1)) return false;
@@ -249,15 +256,20 @@ DEV bool volume_t(const DevScene &S, const Entry &e, const Ray &r, double lo, do
   return true;
 }
 
+#ifndef B200_SPHERE_FASTPATH
+#define B200_SPHERE_FASTPATH 0
+#endif
 // ---------------------------------------------------------------- one leaf entry: accepted t in [lo, hi]
 DEV bool entry_t(const DevScene &S, const Entry &e, const Ray &rw, double lo, double hi, const Stream &st, int bounce, double &t) {
   const int kind = entry_kind(e);
-  if (kind == E_SPHERE && e.kind_chain == (uint32_t)E_SPHERE) return sphere_row_t(S, e.row, false, rw, lo, hi, t); // hot path: untransformed sphere
-  const Ray r = chain_apply(S, entry_chain(e), rw);
+#if B200_SPHERE_FASTPATH
+  if (e.kind_chain == (uint32_t)E_SPHERE) return sphere_row_t(S, e.row, false, rw, lo, hi, t); // hot path: untransformed static sphere
+#endif
+  const Ray r = chain_apply(S, entry_chain(e), rw); // chain 0 (no transform) returns at once
   double a, b;
   switch (kind) {
-  case E_SPHERE: return sphere_row_t(S, e.row, false, r, lo, hi, t);
-  case E_SPHERE_MOVING: return sphere_row_t(S, e.row, true, r, lo, hi, t);
+  case E_SPHERE:
+  case E_SPHERE_MOVING: return sphere_row_t(S, e.row, kind == E_SPHERE_MOVING, r, lo, hi, t); // one inlined copy for both
   case E_QUAD: return quad_row_t(S, e.row, r, lo, hi, t, a, b);
   case E_TRI: return tri_row_t(S, e.row, r, lo, hi, t) && t == t; // a NaN t is a "hit" in the reference; only the mirror traversal reproduces that
   case E_VOLUME: return volume_t(S, e, r, lo, hi, st, bounce, t);
@@ -270,7 +282,10 @@ DEV bool entry_t(const DevScene &S, const Entry &e, const Ray &rw, double lo, do
 // the only texture::sample that looks at u, v: src/texture.h:12-119), which spares the shading kernels acos + atan2 per sphere hit.
 #define B200_UV_ALWAYS 1
 #define B200_UV_IF_USED 2
-DEV bool material_reads_uv(const DevScene &S, int mat) { return S.textures[S.materials[mat].tex].kind == B200RT_TEX_PICTURE; }
+DEV bool material_reads_uv(const DevScene &S, int mat) {
+  const int k = S.textures[S.materials[mat].tex].kind;
+  return k == B200RT_TEX_PICTURE || k == B200RT_TEX_PICTURE_LINEAR;
+}
 
 DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, Rec &rec, int uv_mode = B200_UV_ALWAYS) {
   const int chain = entry_chain(e);

@@ -128,4 +128,33 @@ __global__ void __launch_bounds__(B200_PPM_CTA) k_ppm_write(const int32_t *rgb, 
   }
 }
 
+// ------------------------------------------------------------------------------------------------ binary writers
+// Beside the reference's P3 text: the same pixels as a binary PPM and as an OpenEXR file.
+//   P6 : "P6\nW H\n255\n" + one byte per component = the integer write_color prints (src/color.h:22-36), clamped to
+//        [0, 255] because a byte cannot hold the reference's unclamped values (emitters print > 255, NaN prints INT_MIN).
+//   EXR: the LINEAR image pixel_color / spp (src/camera.h:169) as 32-bit floats, no gamma, no clamp: single-part scan-line
+//        file, NO_COMPRESSION, channels B, G, R (alphabetical, as the format requires), increasing y.  The device writes
+//        every scan-line block {y, byte count, B row, G row, R row} at its final offset; the host writes header + offsets.
+__global__ void __launch_bounds__(256) k_pack_p6(const double *sum, size_t n_comp, double spp, unsigned char *out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_comp; i += (size_t)gridDim.x * blockDim.x) {
+    const int32_t v = ppm_component(sum[i], spp);
+    out[i] = (unsigned char)(v < 0 ? 0 : (v > 255 ? 255 : v));
+  }
+}
+__global__ void __launch_bounds__(256) k_pack_exr(const double *sum, int W, int H, double spp, unsigned char *blocks) {
+  const size_t block_bytes = 8 + (size_t)W * 12, npix = (size_t)W * H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (size_t)gridDim.x * blockDim.x) {
+    const int y = (int)(i / W), x = (int)(i % W);
+    unsigned char *b = blocks + (size_t)y * block_bytes;
+    if (x == 0) {
+      reinterpret_cast<int32_t *>(b)[0] = y;
+      reinterpret_cast<int32_t *>(b)[1] = W * 12;
+    }
+    float *row = reinterpret_cast<float *>(b + 8); // blocks start at a multiple of 4 (the host pads the header)
+    row[x] = (float)(sum[3 * i + 2] / spp);         // B
+    row[(size_t)W + x] = (float)(sum[3 * i + 1] / spp);     // G
+    row[2 * (size_t)W + x] = (float)(sum[3 * i] / spp);     // R
+  }
+}
+
 } // namespace b200

@@ -79,6 +79,7 @@ struct DevScene {
   const double *quads;
   const int32_t *quad_mat;
   const double *tris;
+  const float4 *tri32; // non-null: the nine vertex coordinates of every triangle as binary32 (exactly representable), three float4 per row
   const int32_t *tri_mat;
   const b200rt_volume *volumes;
   const b200rt_material *materials;
@@ -96,6 +97,7 @@ struct DevScene {
   int32_t bvh_root; // child-reference encoding; B200_EMPTY_ROOT for an empty world
   uint32_t n_bvh_nodes;
   const Entry *entries;  // BVH leaf order
+  const uint8_t *entry_queue; // per entry: the shade queue of its material (b200rt_material_kind), so that a finished ray needs ONE load, not entry -> row -> material
   const Entry *bentries; // volume boundaries
   const VolInst *vol_inst;
   const ChainOp *chain_ops;

@@ -30,7 +30,7 @@ DEV double perlin_noise(const double *vec, const int32_t *perm, V p) { // src/no
   const int iu = int(floor(p.x)), iv = int(floor(p.y)), iw = int(floor(p.z));
   return perlin_interp(vec, perm, iu, iv, iw, p.x - iu, p.y - iv, p.z - iw);
 }
-DEV double perlin_turb(const double *vec, const int32_t *perm, int depth, V p) { // src/noise.h:45-55
+DEV_COLD double perlin_turb(const double *vec, const int32_t *perm, int depth, V p) { // src/noise.h:45-55
   double accum = 0;
   V temp_p = p;
   double weight = 1.0;
@@ -42,7 +42,7 @@ DEV double perlin_turb(const double *vec, const int32_t *perm, int depth, V p) {
   return fabs(accum);
 }
 DEV double lerp3(double t, double a, double b) { return (1 - t) * a + t * b; } // src/utility.h:84
-DEV double value_noise(const float *lat, int res, V p) {                         // src/noise.h:106-132
+DEV_COLD double value_noise(const float *lat, int res, V p) {                         // src/noise.h:106-132
   const V fp = vfloor(p);
   const double R = res;
   const float x0y0z0 = lat[(size_t)(fp.x * R * R + fp.y * R + fp.z)];
@@ -64,7 +64,7 @@ DEV V cell_offset(V u) { // worley_noise::get_rand_offset, src/noise.h:141-145 (
   const V res = v3(sin(rv.x), sin(rv.y), sin(rv.z)) * 43758.5453;
   return res - vfloor(res);
 }
-DEV double worley_noise(V p, bool voronoi) { // src/noise.h:147-167, :179-200
+DEV_COLD double worley_noise(V p, bool voronoi) { // src/noise.h:147-167, :179-200
   const V fp = vfloor(p);
   float min_dist = 3.402823466e+38f;
   float colr = 0.0f;
@@ -80,6 +80,18 @@ DEV double worley_noise(V p, bool voronoi) { // src/noise.h:147-167, :179-200
         }
       }
   return voronoi ? (double)colr : (double)(min_dist * min_dist);
+}
+
+// One texel as a colour: 8-bit images as the reference reads them (byte / 256, src/texture.h:72-73), float images (12 or 16
+// bytes per pixel, the opt-in un-quantised ingest) as they are: no clamp, so an HDR environment keeps its values above 1.
+DEV V image_texel(const DevScene &S, const b200rt_image &im, int i, int j) {
+  const uint8_t *px = S.image_bytes + im.offset + ((size_t)j * im.width + i) * im.bytes_per_pixel;
+  if (im.bytes_per_pixel >= 12) {
+    const float *f = reinterpret_cast<const float *>(px);
+    return v3((double)f[0], (double)f[1], (double)f[2]);
+  }
+  const double cs = 1 / 256.0;
+  return v3(px[0] * cs, px[1] * cs, px[2] * cs);
 }
 
 DEV V tex_sample(const DevScene &S, int tex, double u, double v, V p) {
@@ -99,8 +111,20 @@ DEV V tex_sample(const DevScene &S, int tex, double u, double v, V p) {
     int j = (int)(im.height * (1 - v));
     i = i < 0 ? 0 : (i < im.width ? i : im.width - 1);
     j = j < 0 ? 0 : (j < im.height ? j : im.height - 1);
-    const uint8_t *px = S.image_bytes + im.offset + ((size_t)j * im.width + i) * im.bytes_per_pixel;
-    return v3(px[0] * cs, px[1] * cs, px[2] * cs);
+    return image_texel(S, im, i, j);
+  }
+  case B200RT_TEX_PICTURE_LINEAR: { // opt-in: bilinear between texel centres, edges clamped
+    const b200rt_image im = S.images[t.aux];
+    if (!im.has_data) return v3(255 / 256.0, 0.0, 255 / 256.0);
+    const double x = im.width * u - 0.5, y = im.height * (1 - v) - 0.5;
+    const double fx0 = floor(x), fy0 = floor(y);
+    const double ax = x - fx0, ay = y - fy0;
+    const int W = im.width, H = im.height;
+    auto cl = [](double f, int n) { return f < 0 ? 0 : (f > n - 1 ? n - 1 : (int)f); };
+    const int i0 = cl(fx0, W), i1 = cl(fx0 + 1, W), j0 = cl(fy0, H), j1 = cl(fy0 + 1, H);
+    const V c00 = image_texel(S, im, i0, j0), c10 = image_texel(S, im, i1, j0), c01 = image_texel(S, im, i0, j1), c11 = image_texel(S, im, i1, j1);
+    const V top = (1 - ax) * c00 + ax * c10, bot = (1 - ax) * c01 + ax * c11;
+    return (1 - ay) * top + ay * bot;
   }
   case B200RT_TEX_PERLIN: { // src/texture.h:86-88
     const double *vec = S.perlin_vec + (size_t)t.aux * 768;

@@ -67,6 +67,7 @@ struct WaveParams {
   uint64_t seed;
   uint32_t npix, width;
   int32_t spp_begin, max_depth, kill_zero, refill; // refill: idle lanes per warp that trigger a fetch in k_extend_persistent
+  int32_t leaf_lanes; // k_extend_persistent<UNI>: lanes waiting at a leaf that trigger the leaf phase (32 = only when no lane is at a node)
   int32_t fused_miss; // 1 = the scene has no background: a miss adds 0, the extend kernel finishes it itself (no miss queue, no miss launch)
   double bound[3]; // DevScene::bound, for the producers' make_setup
 };
@@ -77,11 +78,25 @@ struct PathHead { // what every consumer needs
 };
 #if B200_PATH_PAIRED
 // one 256-bit access = two adjacent quads; p must be 32-byte aligned
+// B200_STREAM_HINTS=1: the path state is written once and read once per wave and a wave (gigabytes) is far larger than the
+// 126 MB L2, so its lines only push the scene (BVH, primitives: re-read by every ray) out of L2.  They are marked
+// evict-first in L2 and not allocated in L1 (LDG/STG.E.NA.EFL2.256, LDGSTS with an evict-first policy).
+#ifndef B200_STREAM_HINTS
+#define B200_STREAM_HINTS 1
+#endif
 DEV void ld256(const double2 *p, double2 &a, double2 &b) {
+#if B200_STREAM_HINTS
+  asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a.x), "=d"(a.y), "=d"(b.x), "=d"(b.y) : "l"(p));
+#else
   asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a.x), "=d"(a.y), "=d"(b.x), "=d"(b.y) : "l"(p));
+#endif
 }
 DEV void st256(double2 *p, const double2 &a, const double2 &b) {
+#if B200_STREAM_HINTS
+  asm volatile("st.global.L1::no_allocate.L2::evict_first.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a.x), "d"(a.y), "d"(b.x), "d"(b.y) : "memory");
+#else
   asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a.x), "d"(a.y), "d"(b.x), "d"(b.y) : "memory");
+#endif
 }
 DEV double pack2(float lo, float hi) { return __hiloint2double(__float_as_int(hi), __float_as_int(lo)); }
 DEV float unpack_lo(double d) { return __int_as_float(__double2loint(d)); }
@@ -250,6 +265,11 @@ DEV int entry_material(const DevScene &S, const Entry &e) {
   }
 }
 
+__global__ void k_fill_entry_queue(DevScene S, uint8_t *out) { // DevScene::entry_queue
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < S.n_entries) out[i] = (uint8_t)S.materials[entry_material(S, S.entries[i])].kind;
+}
+
 struct Queues {
   uint32_t *q[B200_NQUEUES];
 };
@@ -320,6 +340,23 @@ DEV void cp_async16(void *smem_dst, const void *gmem_src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src));
 #endif
 }
+DEV unsigned long long l2_evict_first_policy() {
+  unsigned long long pol = 0;
+#ifndef B200_HOST_EMU
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+#endif
+  return pol;
+}
+DEV void cp_async16_stream(void *smem_dst, const void *gmem_src, unsigned long long pol) {
+#ifndef B200_HOST_EMU
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+#if B200_STREAM_HINTS
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(d), "l"(gmem_src), "l"(pol));
+#else
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src));
+#endif
+#endif
+}
 DEV void cp_async_commit() {
 #ifndef B200_HOST_EMU
   asm volatile("cp.async.commit_group;");
@@ -358,7 +395,12 @@ DEV void cp_async_wait_all() {
 #ifndef B200_EXT_DYNAMIC
 #define B200_EXT_DYNAMIC 4 // largest number of batches claimed per atomic; 0 = static striding (profiles/r01_v_*)
 #endif
-template <int MAXREG, bool SPEC, int WARPS, int STAGES, bool WIDE>
+// UNI: the traversal loop is WARP-UNIFORM ("threshold if-if"): every iteration the warp votes and then either all lanes that
+// stand at an inner node take one node step, or all lanes that stand at a leaf test it.  The leaf phase is entered when no
+// lane is at a node or when at least wp.leaf_lanes lanes wait at a leaf; leaf_lanes = 32 is the while-while schedule (leaves
+// only when every lane has found one), small values stop lanes that have found their leaf from idling through the node
+// steps of the slowest lane.  Finished lanes refill from the staged batch as before.
+template <int MAXREG, bool SPEC, int WARPS, int STAGES, bool WIDE, bool UNI = false>
 __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, Pools P, HitRef *hits, WaveParams wp) {
   const PathBuf cur = pool_cur(c, P);
 #if B200_PATH_PAIRED
@@ -371,6 +413,7 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
   const unsigned FULL = 0xffffffffu;
   const uint32_t n_warps = gridDim.x * WARPS, n_batches = (n + 31) / 32;
   const int refill = wp.refill, keep = 33 - wp.refill;
+  const unsigned long long stream_pol = l2_evict_first_policy();
 
   auto prefetch = [&](int stg, uint32_t batch) { // one cp.async group per call, also when there is nothing to copy
 #if B200_PATH_PAIRED
@@ -382,9 +425,9 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
 #pragma unroll
         for (int k = 0; k < 2; k++) {
           const uint32_t ch = 32 * k + lane;
-          if (i0 + (ch >> 1) < n) cp_async16(&stage_mem[wib][stg][64 * c + ch], cur.base + ((size_t)c * cur.capacity + i0) * 2 + ch);
+          if (i0 + (ch >> 1) < n) cp_async16_stream(&stage_mem[wib][stg][64 * c + ch], cur.base + ((size_t)c * cur.capacity + i0) * 2 + ch, stream_pol);
         }
-      if (i0 + lane < n) cp_async16(&stage_mem[wib][stg][192 + lane], quad_ptr(cur, 6, i0 + lane)); // q6 only: q7 (throughput) stays in HBM
+      if (i0 + lane < n) cp_async16_stream(&stage_mem[wib][stg][192 + lane], quad_ptr(cur, 6, i0 + lane), stream_pol); // q6 only: q7 (throughput) stays in HBM
     }
 #else
     const uint32_t i = batch * 32 + lane;
@@ -526,6 +569,33 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
       if (count == 0) break;
       continue;
     }
+    if (UNI) {
+      const int T = wp.leaf_lanes;
+      for (;;) {
+        const bool at_node = active && node >= 0, at_leaf = active && node < 0; // active lanes never hold B200_DONE here
+        const unsigned mn = __ballot_sync(FULL, at_node), ml = __ballot_sync(FULL, at_leaf);
+        if ((mn | ml) == 0u) break;
+        if (count > 0 && 32 - __popc(mn | ml) >= refill) break; // enough finished lanes: take new rays first
+        if (mn != 0u && __popc(ml) < T) {
+          if (at_node) {
+            node = WIDE ? node_step4(S, node, rs, lo32, hi32, stack, sp) : node_step(S, node, rs, lo32, hi32, stack, sp);
+            if (node == B200_DONE && sp > 0) node = stack[--sp];
+          }
+        } else if (at_leaf) {
+          leaf_test(S, node, r, 0.001, B200_INF, st, bounce, best);
+          if (best.entry >= 0) hi32 = __double2float_ru(best.t * rs.tsc);
+          node = sp > 0 ? stack[--sp] : B200_DONE;
+        }
+        if (active && node == B200_DONE) {
+          if (best.entry < 0)
+            finish_miss(idx);
+          else
+            store_hit(hits, idx, best.t, best.entry, S.entry_queue[best.entry]);
+          active = false;
+        }
+      }
+      continue;
+    }
     while (active) {
       if (SPEC) {
         int32_t pending = B200_DONE;
@@ -564,7 +634,7 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
         if (best.entry < 0)
           finish_miss(idx);
         else
-          store_hit(hits, idx, best.t, best.entry, S.materials[entry_material(S, S.entries[best.entry])].kind);
+          store_hit(hits, idx, best.t, best.entry, S.entry_queue[best.entry]);
         active = false;
       } else if (count > 0 && __popc(__activemask()) < keep) {
         break;

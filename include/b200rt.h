@@ -107,7 +107,9 @@ typedef enum b200rt_texture_kind {
   B200RT_TEX_PERLIN = 3,  /* src/texture.h:80-93   aux = perlin table index, scale */
   B200RT_TEX_VALUE = 4,   /* src/texture.h:95-103  aux = value-noise index */
   B200RT_TEX_WORLEY = 5,  /* src/texture.h:105-111 */
-  B200RT_TEX_VORONOI = 6  /* src/texture.h:113-119 */
+  B200RT_TEX_VORONOI = 6, /* src/texture.h:113-119 */
+  B200RT_TEX_PICTURE_LINEAR = 7 /* NOT in the reference (opt-in): picture_texture with bilinear filtering between
+                                   texel centres, edges clamped; aux = image index.  The reference's lookup is nearest (src/texture.h:67-74) */
 } b200rt_texture_kind;
 
 typedef struct b200rt_texture {
@@ -121,7 +123,9 @@ typedef struct b200rt_texture {
 typedef struct b200rt_image { /* src/image.h:85-90; bytes are image::bdata, already 8-bit linear */
   int32_t width;
   int32_t height;
-  int32_t bytes_per_pixel; /* 3 (stb) or 4 (EXR) */
+  int32_t bytes_per_pixel; /* 3 (stb) or 4 (EXR): the reference's 8-bit image::bdata, read as byte / 256 (src/texture.h:72-73).
+                              12 or 16: 3 or 4 binary32 channels per pixel = image::fdata, un-quantised and unclamped (opt-in:
+                              the reference always quantises, src/image.h:99-117); offset must then be a multiple of 4 */
   int32_t has_data;        /* 0: bdata == nullptr, lookups give magenta (src/image.h:75-76) */
   uint64_t offset;         /* into image_bytes */
 } b200rt_image;
@@ -235,6 +239,14 @@ typedef enum b200rt_option {
                                  the wave until no path is alive and no sample is left (no host round trip; the call returns without waiting unless
                                  statistics are requested); 0 = the host, reading the counters back (the mode that can time single launches:
                                  b200rt_stats::extend_ms).  The mirror traversal always uses the host loop */
+  B200RT_OPT_EXTEND_LOOP = 17, /* tuning: loop structure of the persistent extend kernel: 0 = while-while (inner nodes until every lane of the warp has
+                                  found a leaf, then the leaves), 1 = warp-uniform "threshold if-if": the leaf phase starts as soon as
+                                  B200RT_OPT_LEAF_LANES lanes wait at a leaf */
+  B200RT_OPT_LEAF_LANES = 18,  /* tuning: see B200RT_OPT_EXTEND_LOOP (1..32, default 8; 32 = the while-while schedule) */
+  B200RT_OPT_L2_PERSIST = 19,  /* 1 (default): the tree, the leaf entries and the primitive rows are uploaded into one address range that the render
+                                  kernels declare as a persisting L2 access-policy window (the wave's path state streams past it) */
+  B200RT_OPT_TRI_F32 = 20,     /* 1 (default): triangle vertices are kept as 48-byte binary32 rows when every coordinate is exactly representable
+                                  (glTF positions are), and widened after the load: identical binary64 operands, 40 % fewer bytes per test */
   B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 8 from 32 Ki BVH nodes) */
 } b200rt_option;
 
@@ -308,6 +320,16 @@ int b200rt_finalize(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, doubl
  * b200rt_ppm_bound(W, H) always suffices; a smaller one fails with B200RT_ERR_INVALID and *out_len = the size needed. */
 size_t b200rt_ppm_bound(int image_width, int image_height);
 int b200rt_format_ppm(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, char *out, size_t capacity, size_t *out_len);
+
+/* The same output stage in other containers ("binary PPM/EXR writer beside the reference's P3 text").
+ *   B200RT_IMAGE_PPM_TEXT   = b200rt_format_ppm: the reference's own file (src/camera.h:149-151, 174)
+ *   B200RT_IMAGE_PPM_BINARY   "P6\nW H\n255\n" + one byte per component: the integer write_color prints (src/color.h:22-36), clamped to [0, 255]
+ *   B200RT_IMAGE_EXR          OpenEXR, single part, scan lines, no compression, 32-bit float B G R: the LINEAR image pixel_color / spp
+ *                             (src/camera.h:169), no gamma, no clamp (emitters and NaNs survive)
+ * Pixel conversion and file layout run on the device; `out` receives the complete file image; b200rt_image_bound() always suffices. */
+typedef enum b200rt_image_format { B200RT_IMAGE_PPM_TEXT = 0, B200RT_IMAGE_PPM_BINARY = 1, B200RT_IMAGE_EXR = 2 } b200rt_image_format;
+size_t b200rt_image_bound(int format, int image_width, int image_height);
+int b200rt_format_image(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, int format, char *out, size_t capacity, size_t *out_len);
 
 /* Replaces: texture::sample(u, v, p) (src/texture.h:9) of texture row `tex` on a batch.
  * uvp5 = n x {u, v, p[3]}, rgb = n x 3.  Host buffers. */

@@ -122,6 +122,10 @@ struct flat_scene {
 
 class flattener {
 public:
+  // Opt-ins that deliberately leave the reference's texture semantics (both default off = the reference's own lookups):
+  bool float_images = false;      // hand image::fdata (un-quantised binary32) to the backend instead of the 8-bit image::bdata
+  bool bilinear_pictures = false; // picture_texture lookups filter bilinearly instead of picking the nearest texel (src/texture.h:67-74)
+public:
   flat_scene out;
 
   // world / light / background exactly as handed to camera::render (src/camera.h:135, :329).
@@ -368,7 +372,7 @@ public:
       for (int k = 0; k < 3; k++) d.c0[k] = x->odd_.e[k], d.c1[k] = x->even_.e[k];
       d.scale = x->scale_;
     } else if (auto x = dynamic_cast<const picture_texture *>(t)) {
-      d.kind = B200RT_TEX_PICTURE;
+      d.kind = bilinear_pictures ? B200RT_TEX_PICTURE_LINEAR : B200RT_TEX_PICTURE;
       d.aux = image_row(x->image_.get());
     } else if (auto x = dynamic_cast<const perlin_texture *>(t)) {
       d.kind = B200RT_TEX_PERLIN;
@@ -413,7 +417,18 @@ public:
     b200rt_image d;
     std::memset(&d, 0, sizeof d);
     d.has_data = (im->bdata != nullptr && im->fdata != nullptr) ? 1 : 0;
-    if (d.has_data) {
+    if (d.has_data && float_images) {
+      // opt-in: the image as the decoder delivered it, image::fdata (src/image.h:85-86), binary32 per channel,
+      // instead of the 8-bit copy the reference samples (src/image.h:99-117): an HDR environment keeps its values above 1
+      d.width = im->image_width;
+      d.height = im->image_height;
+      d.bytes_per_pixel = im->bytes_per_pixel * 4; // 3 channels (stb) -> 12, 4 channels (EXR) -> 16
+      d.offset = out.image_bytes.size();
+      size_t n = (size_t)im->image_width * im->image_height * im->bytes_per_pixel * sizeof(float);
+      const unsigned char *src = reinterpret_cast<const unsigned char *>(im->fdata);
+      out.image_bytes.insert(out.image_bytes.end(), src, src + n);
+      while (out.image_bytes.size() % 16) out.image_bytes.push_back(0);
+    } else if (d.has_data) {
       d.width = im->image_width;
       d.height = im->image_height;
       d.bytes_per_pixel = im->bytes_per_pixel;

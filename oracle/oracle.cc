@@ -385,6 +385,18 @@ double worley_noise(V p, bool voronoi) { // src/noise.h:147-167 and :179-200
 }
 
 // ------------------------------------------------------------------ textures (src/texture.h)
+// 8-bit texels as the reference reads them (byte / 256, src/texture.h:72-73); float texels (the opt-in ingest) as they are
+V image_texel(const Scene &s, const b200rt_image &im, int i, int j) {
+  const uint8_t *px = s.d->image_bytes + im.offset + ((size_t)j * im.width + i) * im.bytes_per_pixel;
+  if (im.bytes_per_pixel >= 12) {
+    float f[3];
+    std::memcpy(f, px, 12);
+    return v3((double)f[0], (double)f[1], (double)f[2]);
+  }
+  double cs = 1 / 256.0;
+  return v3(px[0] * cs, px[1] * cs, px[2] * cs);
+}
+
 V tex_sample(const Scene &s, int tex, double u, double v, V p) {
   const b200rt_texture &t = s.d->textures[tex];
   switch (t.kind) {
@@ -403,9 +415,19 @@ V tex_sample(const Scene &s, int tex, double u, double v, V p) {
     auto clampi = [](int x, int low, int high) { return x < low ? low : (x < high ? x : high - 1); };
     i = clampi(i, 0, im.width);
     j = clampi(j, 0, im.height);
-    const uint8_t *px = s.d->image_bytes + im.offset + (size_t)j * im.width * im.bytes_per_pixel + (size_t)i * im.bytes_per_pixel;
-    double cs = 1 / 256.0;
-    return v3(px[0] * cs, px[1] * cs, px[2] * cs);
+    return image_texel(s, im, i, j);
+  }
+  case B200RT_TEX_PICTURE_LINEAR: { // the backend's own opt-in (not in the reference): bilinear between texel centres, clamped edges
+    const b200rt_image &im = s.d->images[t.aux];
+    if (!im.has_data) return v3(255 / 256.0, 0.0, 255 / 256.0);
+    double x = im.width * u - 0.5, y = im.height * (1 - v) - 0.5;
+    double fx0 = std::floor(x), fy0 = std::floor(y);
+    double ax = x - fx0, ay = y - fy0;
+    auto cl = [](double f, int n) { return f < 0 ? 0 : (f > n - 1 ? n - 1 : (int)f); };
+    int i0 = cl(fx0, im.width), i1 = cl(fx0 + 1, im.width), j0 = cl(fy0, im.height), j1 = cl(fy0 + 1, im.height);
+    V c00 = image_texel(s, im, i0, j0), c10 = image_texel(s, im, i1, j0), c01 = image_texel(s, im, i0, j1), c11 = image_texel(s, im, i1, j1);
+    V top = (1 - ax) * c00 + ax * c10, bot = (1 - ax) * c01 + ax * c11;
+    return (1 - ay) * top + ay * bot;
   }
   case B200RT_TEX_PERLIN: { // :86-88
     const double *vec = s.d->perlin_vec + (size_t)t.aux * 768;

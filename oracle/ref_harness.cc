@@ -674,6 +674,24 @@ int ref_scene_create(const char *name, int width, int spp, int depth, const char
   }
 }
 
+// Flatten the same live objects again with the adaptor's texture opt-ins (include/b200rt_adaptor.hpp: flattener::float_images,
+// ::bilinear_pictures); the description returned by ref_scene_desc changes accordingly.  0/0 restores the reference semantics.
+int ref_scene_reflatten(int h, int float_images, int bilinear) {
+  scene *s = get(h);
+  if (!s) return -1;
+  try {
+    s->flat = b200::flattener();
+    s->flat.float_images = float_images != 0;
+    s->flat.bilinear_pictures = bilinear != 0;
+    s->flat.run(*s->world, s->light.get(), s->cam.background_.get());
+    s->desc = s->flat.out.desc();
+    return 0;
+  } catch (const std::exception &e) {
+    t_err = e.what();
+    return -1;
+  }
+}
+
 void ref_scene_destroy(int h) {
   std::lock_guard<std::mutex> lk(g_mu);
   g_scenes.erase(h);

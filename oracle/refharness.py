@@ -218,3 +218,17 @@ def write_colors(rgb):
     buf = np.empty(n, np.uint8)
     L.ref_write_colors(rgb.ctypes.data, W, H, buf.ctypes.data, n)
     return buf.tobytes()
+
+
+def _reflatten(self, float_images=False, bilinear=False):
+    """The same live reference objects flattened with the adaptor's texture opt-ins -> Scene (the handle's description changes too)."""
+    L = lib()
+    L.ref_scene_reflatten.argtypes = [C.c_int, C.c_int, C.c_int]
+    if L.ref_scene_reflatten(self.h, int(float_images), int(bilinear)) != 0:
+        raise RuntimeError("ref_scene_reflatten: " + L.ref_last_error().decode())
+    sc = Scene.from_desc_pointer(L.ref_scene_desc(self.h))
+    sc.name = self.name
+    return sc
+
+
+RefScene.reflatten = _reflatten

@@ -265,3 +265,180 @@ def test_max_depth_zero_renders_black(ctx, depth, build_oracle):
     want = build_oracle.render(g.scene, cam, 5, 0, 4)
     assert not img.any() and not want["sum"].any()
     assert st["samples"] == want["stats"]["samples"] == 4 * cam.image_width * cam.image_height and st["rays"] == want["stats"]["rays"] == 0
+
+
+# ------------------------------------------------------------------------------------------------ several GPUs inside the boundary
+def _n_gpus():
+    import torch
+
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("n", [1, 2, 4, 8])
+@pytest.mark.parametrize("reduce_mode", [abi.GROUP_REDUCE_NCCL, abi.GROUP_REDUCE_PEER])
+def test_group_render_equals_single_device(ctx, n, reduce_mode):
+    """b200rt_group_render over n devices (sample-range split, one ncclReduce or one peer-load kernel) == b200rt_render on one
+    device: same samples whatever n is (Philox streams are keyed by the global sample index), sums equal up to fp64 addition order."""
+    if n > _n_gpus():
+        pytest.skip(f"needs {n} GPUs")
+    g = golden("rtow")
+    cam = g.cam_full.copy()
+    cam.image_width, cam.image_height = 320, 180
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(cam)
+    want, st1 = ctx.render(77, 3, 3 + 21)
+    with pkg.backend.Group(list(range(n))) as grp:
+        grp.set_option(abi.GROUP_OPT_REDUCE, reduce_mode)
+        grp.upload_scene(g.scene)
+        grp.set_camera(cam)
+        got, st = grp.render(77, 3, 3 + 21)
+        assert (st["samples"], st["rays"]) == (st1["samples"], st1["rays"])
+        assert np.allclose(got, want, rtol=1e-12, atol=1e-12) and want.sum() > 0
+        again, _ = grp.render(77, 3, 3 + 21)  # a second frame through the same group (cached wave graphs, reused communicators)
+        assert np.allclose(again, want, rtol=1e-12, atol=1e-12)
+        fewer, st2 = grp.render(77, 0, 1)  # fewer samples than devices: some members render nothing
+        one, _ = ctx.render(77, 0, 1)
+        assert np.allclose(fewer, one, rtol=1e-12, atol=1e-12) and st2["samples"] == 320 * 180
+        if n > 1:
+            print(f"[group x{n}, reduce {reduce_mode}] {grp.reduce_backend()}")
+
+
+def test_group_errors_are_loud():
+    with pytest.raises(pkg.backend.B200RTError):
+        pkg.backend.Group([0, 0])
+    with pytest.raises(pkg.backend.B200RTError):
+        pkg.backend.Group([99])
+    with pkg.backend.Group([0]) as grp:
+        with pytest.raises(pkg.backend.B200RTError):
+            grp.render(1, 0, 1) if grp.camera else grp._check(grp._lib.b200rt_group_render(grp._h, 1, 0, 1, np.zeros(3).ctypes.data, None))
+
+
+# ------------------------------------------------------------------------------------------------ binary writers (SURVEY.md 8f rank 2)
+def _parse_exr(buf):
+    """Minimal reader for what b200rt_format_image writes (single part, scan lines, NO_COMPRESSION, FLOAT channels)."""
+    import struct
+
+    assert buf[:4] == bytes([0x76, 0x2F, 0x31, 0x01]) and struct.unpack("<I", buf[4:8])[0] == 2
+    pos, attrs = 8, {}
+    while buf[pos] != 0:
+        e = buf.index(b"\0", pos)
+        name = buf[pos:e].decode()
+        pos = e + 1
+        e = buf.index(b"\0", pos)
+        typ = buf[pos:e].decode()
+        pos = e + 1
+        (size,) = struct.unpack("<i", buf[pos:pos + 4])
+        attrs[name] = (typ, buf[pos + 4:pos + 4 + size])
+        pos += 4 + size
+    pos += 1
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1])
+    W, H = x1 - x0 + 1, y1 - y0 + 1
+    assert attrs["compression"][1] == b"\0" and attrs["lineOrder"][1] == b"\0"
+    names, ch = [], attrs["channels"][1]
+    p = 0
+    while ch[p] != 0:
+        e = ch.index(b"\0", p)
+        names.append(ch[p:e].decode())
+        assert struct.unpack("<i", ch[e + 1:e + 5])[0] == 2  # FLOAT
+        p = e + 17
+    offs = np.frombuffer(buf, "<u8", H, pos)
+    img = np.zeros((H, W, len(names)), np.float32)
+    for y in range(H):
+        yy, nbytes = struct.unpack("<2i", buf[offs[y]:offs[y] + 8])
+        assert yy == y0 + y and nbytes == 4 * W * len(names)
+        img[y] = np.frombuffer(buf, "<f4", W * len(names), offs[y] + 8).reshape(len(names), W).T
+    return names, img
+
+
+def test_binary_ppm_and_exr_writers(ctx, tmp_path):
+    """P6: the bytes are the integers write_color prints (src/color.h:22-36), clamped to a byte.  EXR: the linear image
+    pixel_color / spp as float32, readable by an independent decoder (OpenCV, where its OpenEXR codec is enabled)."""
+    g = golden("cornell")
+    for W, H in ((37, 29), (1, 1), (640, 3)):
+        cam = g.cam_small.copy()
+        cam.image_width, cam.image_height = W, H
+        ctx.set_camera(cam)
+        rng = np.random.RandomState(W)
+        s = rng.rand(H, W, 3) * 10 ** rng.uniform(-3, 3, size=(H, W, 3))
+        s.reshape(-1)[:3] = [np.nan, -3.0, 1e300]
+        _, ppm = ctx.finalize(s, 16, want_ppm=True)
+        p6 = ctx.format_image(s, 16, abi.IMAGE_PPM_BINARY)
+        head = f"P6\n{W} {H}\n255\n".encode()
+        assert p6[: len(head)] == head and len(p6) == len(head) + W * H * 3
+        assert np.array_equal(np.frombuffer(p6, np.uint8, offset=len(head)), np.clip(ppm, 0, 255).astype(np.uint8).reshape(-1))
+        assert ctx.format_image(s, 16, abi.IMAGE_PPM_TEXT) == ctx.format_ppm(s, 16)
+        exr = ctx.format_image(s, 16, abi.IMAGE_EXR)
+        names, img = _parse_exr(exr)
+        assert names == ["B", "G", "R"]
+        with np.errstate(over="ignore"):
+            want = (s / 16).astype(np.float32)
+        assert same(img[..., ::-1], want).all()
+        with pytest.raises(pkg.backend.B200RTError):
+            ctx.format_image(s, 16, abi.IMAGE_EXR, capacity=len(exr) - 1)
+        if (W, H) == (37, 29):
+            os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+            try:
+                import cv2
+
+                path = str(tmp_path / "frame.exr")
+                open(path, "wb").write(exr)
+                back = cv2.imread(path, cv2.IMREAD_UNCHANGED)
+            except Exception as e:  # OpenCV built without the codec
+                back = None
+                print(f"[exr] OpenCV could not decode: {e}")
+            if back is not None:
+                fin = np.isfinite(want)
+                assert back.shape == (H, W, 3) and np.array_equal(back[..., ::-1][fin], want[fin])
+                print("[exr] decoded by OpenCV's OpenEXR codec: identical")
+    ctx.set_camera(g.cam_small)
+
+
+# ------------------------------------------------------------------------------------------------ float images / bilinear lookups (SURVEY.md 8f rank 4)
+def test_float_images_and_bilinear_lookups(ctx, build_oracle):
+    """The opt-in texture path (not in the reference; the reference path stays the default): (1) a float copy of an 8-bit image
+    gives the reference's own nearest lookups bit for bit; (2) bilinear lookups equal the oracle's restatement bit for bit (no
+    libm involved) on 8-bit and float images; (3) a frame rendered with the float + bilinear variants stays within Monte-Carlo
+    distance of the reference-path frame (same samples, slightly different texels)."""
+    import copy
+
+    images = pkg.images
+    g = golden("light_earth")
+    s = copy.copy(g.scene)
+    s.textures, s.images, s.image_bytes = g.scene.textures.copy(), g.scene.images.copy(), g.scene.image_bytes.copy()
+    tex = int(np.nonzero(s.textures["kind"] == abi.TEX_PICTURE)[0][0])
+    rows = g["tex_rows"] == tex
+    uvp, ref = g["tex_uvp"][rows], g["tex_rgb"][rows]
+    s.textures["aux"][tex] = images.float_copy_of_image(s, int(s.textures["aux"][tex]))
+    ctx.upload_scene(s)
+    assert same(ctx.texture_sample(tex, uvp), ref).all()
+    rng = np.random.RandomState(4)
+    uvp2 = np.concatenate([rng.uniform(-0.1, 1.1, size=(4000, 2)), rng.normal(size=(4000, 3))], axis=1)
+    for image_kind in ("float", "u8"):
+        if image_kind == "u8":
+            s.textures["aux"][tex] = g.scene.textures["aux"][tex]
+        images.set_picture_filter(s, tex, True)
+        ctx.upload_scene(s)
+        got, want = ctx.texture_sample(tex, uvp2), build_oracle.texture_sample(s, tex, uvp2)
+        assert same(got, want).all(), image_kind
+        images.set_picture_filter(s, tex, False)
+    # an HDR value survives: no clamp, no quantisation
+    hdr = np.full((2, 2, 3), 7.25, np.float32)
+    s.textures["aux"][tex] = images.add_image(s, hdr)
+    ctx.upload_scene(s)
+    assert same(ctx.texture_sample(tex, uvp2[:16]), np.full((16, 3), 7.25)).all()
+    # frames
+    ctx.upload_scene(g.scene)
+    ctx.set_camera(g.cam_small)
+    base, _ = ctx.render(9, 0, 64)
+    s.textures["aux"][tex] = images.float_copy_of_image(s, int(g.scene.textures["aux"][tex]))
+    images.set_picture_filter(s, tex, True)
+    ctx.upload_scene(s)
+    lin, _ = ctx.render(9, 0, 64)
+    fin = np.isfinite(base) & np.isfinite(lin)
+    assert abs(lin[fin].mean() - base[fin].mean()) < 0.02 * base[fin].mean()
+    with pytest.raises(pkg.backend.B200RTError):  # float rows must be 4-byte aligned
+        bad = copy.copy(s)
+        bad.images = s.images.copy()
+        bad.images["offset"][-1] += 1
+        ctx.upload_scene(bad)
+    ctx.upload_scene(g.scene)

@@ -250,9 +250,13 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
     base, st = ctx.render(77, 0, 6)
     try:
         for opts in ({abi.OPT_SPECULATIVE_LEAF: 1}, {abi.OPT_REFILL_LANES: 12}, {abi.OPT_SPECULATIVE_LEAF: 1, abi.OPT_REFILL_LANES: 20}, {abi.OPT_FUSE_MISS: 0},
-                     {abi.OPT_EXTEND_BLOCKS: 9}, {abi.OPT_EXTEND_STAGES: 1}, {abi.OPT_SMEM_CARVEOUT: 100}):
+                     {abi.OPT_EXTEND_BLOCKS: 9}, {abi.OPT_EXTEND_STAGES: 1}, {abi.OPT_SMEM_CARVEOUT: 100}, {abi.OPT_WAVE_LOOP: 0},
+                     {abi.OPT_EXTEND_LOOP: 1}, {abi.OPT_EXTEND_LOOP: 1, abi.OPT_LEAF_LANES: 1}, {abi.OPT_EXTEND_LOOP: 1, abi.OPT_LEAF_LANES: 32, abi.OPT_REFILL_LANES: 8},
+                     {abi.OPT_EXTEND_LOOP: 1, abi.OPT_BVH_WIDTH: 4}):
             for k, v in opts.items():
                 ctx.set_option(k, v)
+            if abi.OPT_BVH_WIDTH in opts:  # takes effect at upload
+                ctx.upload_scene(g.scene)
             img, st2 = ctx.render(77, 0, 6)
             ctx.set_option(abi.OPT_SPECULATIVE_LEAF, 0)
             ctx.set_option(abi.OPT_REFILL_LANES, 0)
@@ -260,6 +264,12 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
             ctx.set_option(abi.OPT_EXTEND_BLOCKS, 4)
             ctx.set_option(abi.OPT_EXTEND_STAGES, 2)
             ctx.set_option(abi.OPT_SMEM_CARVEOUT, -1)
+            ctx.set_option(abi.OPT_WAVE_LOOP, 1)
+            ctx.set_option(abi.OPT_EXTEND_LOOP, 0)
+            ctx.set_option(abi.OPT_LEAF_LANES, 8)
+            if abi.OPT_BVH_WIDTH in opts:
+                ctx.set_option(abi.OPT_BVH_WIDTH, 0)
+                ctx.upload_scene(g.scene)
             assert st2["rays"] == st["rays"], opts
             fin = np.isfinite(base)
             assert np.array_equal(fin, np.isfinite(img))
@@ -271,6 +281,10 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
         ctx.set_option(abi.OPT_EXTEND_BLOCKS, 4)
         ctx.set_option(abi.OPT_EXTEND_STAGES, 2)
         ctx.set_option(abi.OPT_SMEM_CARVEOUT, -1)
+        ctx.set_option(abi.OPT_WAVE_LOOP, 1)
+        ctx.set_option(abi.OPT_EXTEND_LOOP, 0)
+        ctx.set_option(abi.OPT_LEAF_LANES, 8)
+        ctx.set_option(abi.OPT_BVH_WIDTH, 0)
 
 
 def test_white_furnace_known_answer(ctx):

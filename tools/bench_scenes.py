@@ -76,6 +76,7 @@ def main():
     ap.add_argument("--width", type=int, default=0, help="BVH width: 0 = automatic, 2, 4")
     ap.add_argument("--pipelines", type=int, default=2, help="independent wavefronts on two streams (1 also reports the extend share)")
     ap.add_argument("--tail", type=int, default=-1, help="B200RT_OPT_TAIL_PATHS (-1 = library default, 0 = off)")
+    ap.add_argument("--opt", action="append", default=[], help="any b200rt_option as NUMBER=VALUE (repeatable), e.g. --opt 17=1 --opt 18=8")
     ap.add_argument("--mirror", action="store_true", help="also time the node-for-node mirror traversal (parity arbiter)")
     args = ap.parse_args()
     ctx = pkg.backend.Context(0)
@@ -84,6 +85,9 @@ def main():
     ctx.set_option(abi.OPT_PIPELINES, args.pipelines)
     if args.tail >= 0:
         ctx.set_option(abi.OPT_TAIL_PATHS, args.tail)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        ctx.set_option(int(k), float(v))
     for name in args.scenes.split(","):
         t0 = time.perf_counter()
         sc, cam = load(name)
@@ -101,7 +105,7 @@ def main():
             _, st = ctx.render(1, 0, spp)
             if best is None or st["gpu_ms"] < best["gpu_ms"]:
                 best = st
-        line = {"scene": name, "builder": "device LBVH" if args.builder else "host SAH", "config": CONFIGS[name], "width": cam.image_width, "height": cam.image_height, "spp_timed": spp,
+        line = {"scene": name, "opts": args.opt, "builder": "device LBVH" if args.builder else "host SAH", "config": CONFIGS[name], "width": cam.image_width, "height": cam.image_height, "spp_timed": spp,
                 "spp_config": cam.samples_per_pixel, "max_depth": cam.max_depth, "mrays_per_s": best["rays"] / best["gpu_ms"] / 1e3,
                 "msamples_per_s": best["samples"] / best["gpu_ms"] / 1e3, "rays_per_sample": best["rays"] / best["samples"],
                 "gpu_ms": best["gpu_ms"], "extend_share": (best["extend_ms"] / best["gpu_ms"]) if best["extend_ms"] > 0 else None, "waves": best["waves"],
