@@ -133,6 +133,7 @@ struct b200rt_ctx {
   int tri_f32 = 1;     // B200RT_OPT_TRI_F32
   size_t hot_bytes = 0; // prefix of the scene arena that the traversal reads per node / leaf
   size_t l2_window_max = 0, l2_persist_max = 0;
+  int octant_sort = 0; // B200RT_OPT_OCTANT_SORT
   int extend_loop = 0; // B200RT_OPT_EXTEND_LOOP: 0 = while-while, 1 = warp-uniform threshold if-if
   int leaf_lanes = 8;  // B200RT_OPT_LEAF_LANES
   int wave_loop = 1; // B200RT_OPT_WAVE_LOOP: 1 = device-driven CUDA-graph while loop, 0 = host-driven loop with read-backs
@@ -399,6 +400,7 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     return B200RT_OK;
   case B200RT_OPT_L2_PERSIST: c->l2_persist = value != 0; return B200RT_OK;
   case B200RT_OPT_TRI_F32: c->tri_f32 = value != 0; return B200RT_OK; // takes effect at the next b200rt_upload_scene
+  case B200RT_OPT_OCTANT_SORT: c->octant_sort = value != 0; return B200RT_OK;
   case B200RT_OPT_EXTEND_LOOP:
     if (value != 0 && value != 1) return fail(B200RT_ERR_INVALID, "extend loop must be 0 (while-while) or 1 (warp-uniform)");
     c->extend_loop = (int)value;
@@ -539,6 +541,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   UP(d->sphere_mat, d->n_spheres, &S.sphere_mat, "sphere_mat");
   UP(d->quad_mat, d->n_quads, &S.quad_mat, "quad_mat");
   UP(d->tri_mat, d->n_tris, &S.tri_mat, "tri_mat");
+  if (d->tri_uv) UP(d->tri_uv, (size_t)d->n_tris * 6, &S.tri_uv, "tri_uv");
   UP(d->volumes, d->n_volumes, &S.volumes, "volumes");
   UP(d->materials, d->n_materials, &S.materials, "materials");
   UP(d->textures, d->n_textures, &S.textures, "textures");
@@ -573,6 +576,12 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
     if (S.n_entries) k_fill_entry_queue<<<(int)((S.n_entries + 255) / 256), 256, 0, c->stream>>>(S, eq);
     CU(cudaGetLastError());
     S.entry_queue = eq;
+  }
+  { // the structure itself in global memory, for out-of-line device functions (DevScene::self)
+    DevScene *self = nullptr;
+    CU(c->scene_mem.alloc((void **)&self, sizeof(DevScene)));
+    S.self = self;
+    CU(cudaMemcpyAsync(self, &S, sizeof(DevScene), cudaMemcpyHostToDevice, c->stream));
   }
   CU(cudaStreamSynchronize(c->stream)); // host vectors go out of scope
   c->S = S;
@@ -991,6 +1000,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     q.kill_zero = c->kill_zero;
     q.fused_miss = (mirror || !c->fuse_miss) ? 0 : c->bg_mode;
     q.leaf_lanes = c->leaf_lanes;
+    q.octant_sort = c->octant_sort;
     q.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 8 : 32);
     for (int k = 0; k < 3; k++) q.bound[k] = c->S.bound[k];
     tot[p] = (unsigned long long)npix * (unsigned long long)(hi - lo);

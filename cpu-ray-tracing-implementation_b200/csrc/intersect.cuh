@@ -213,7 +213,7 @@ DEV bool tri_row_t(const DevScene &S, int row, const Ray &r, double lo, double h
 }
 
 // ---------------------------------------------------------------- volume boundary: closest t over its leaves
-DEV_COLD bool boundary_t(const DevScene &S, const VolInst &vi, const Ray &r, double lo, double hi, double &tout) {
+DEV bool boundary_t(const DevScene &S, const VolInst &vi, const Ray &r, double lo, double hi, double &tout) {
   bool any = false;
   double best = hi;
   for (int k = 0; k < vi.bcount; k++) {
@@ -238,7 +238,10 @@ DEV_COLD bool boundary_t(const DevScene &S, const VolInst &vi, const Ray &r, dou
 }
 
 // volumne::hit, src/volumne.h:18-46.  `r` is the ray in the volume's own frame.
-DEV_COLD bool volume_t(const DevScene &S, const Entry &e, const Ray &r, double lo, double hi, const Stream &st, int bounce, double &t) {
+// DEV_COLD = inlined by default (see vec.cuh: the out-of-line variant was measured slower); takes the scene through
+// DevScene::self so that the experiment does not force a local-memory copy of the kernel parameter.
+DEV_COLD bool volume_t(const DevScene *Sp, const Entry &e, const Ray &r, double lo, double hi, const Stream &st, int bounce, double &t) {
+  const DevScene &S = *Sp;
   const VolInst vi = S.vol_inst[e.row];
   double t1, t2;
   if (!boundary_t(S, vi, r, -B200_INF, B200_INF, t1)) return false;
@@ -272,7 +275,7 @@ DEV bool entry_t(const DevScene &S, const Entry &e, const Ray &rw, double lo, do
   case E_SPHERE_MOVING: return sphere_row_t(S, e.row, kind == E_SPHERE_MOVING, r, lo, hi, t); // one inlined copy for both
   case E_QUAD: return quad_row_t(S, e.row, r, lo, hi, t, a, b);
   case E_TRI: return tri_row_t(S, e.row, r, lo, hi, t) && t == t; // a NaN t is a "hit" in the reference; only the mirror traversal reproduces that
-  case E_VOLUME: return volume_t(S, e, r, lo, hi, st, bounce, t);
+  case E_VOLUME: return volume_t(S.self, e, r, lo, hi, st, bounce, t);
   }
   return false;
 }
@@ -321,6 +324,16 @@ DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, 
     const double *q = S.tris + (size_t)e.row * B200RT_TRI_STRIDE;
     set_face_normal(rec, r, v3(q[9], q[10], q[11]));
     rec.mat = S.tri_mat[e.row];
+    if (S.tri_uv && (uv_mode == B200_UV_ALWAYS || material_reads_uv(S, rec.mat))) {
+      // opt-in: vertex texture coordinates weighted with moller_trumbore's b0, b1 (src/triangle.h:8-15), recomputed for the hit
+      const V p0 = v3(q[0], q[1], q[2]), p1 = v3(q[3], q[4], q[5]), p2 = v3(q[6], q[7], q[8]);
+      const V e1 = p1 - p0, e2 = p2 - p0, sv = r.o - p0;
+      const V s1 = cross(r.d, e2), s2 = cross(sv, e1);
+      const double det = dot(s1, e1), b0 = dot(s1, sv) / det, b1 = dot(s2, r.d) / det;
+      const double *w = S.tri_uv + (size_t)e.row * 6;
+      rec.u = (1 - b0 - b1) * w[0] + b0 * w[2] + b1 * w[4];
+      rec.v = (1 - b0 - b1) * w[1] + b0 * w[3] + b1 * w[5];
+    }
     break;
   }
   default: { // E_VOLUME, src/volumne.h:41-44

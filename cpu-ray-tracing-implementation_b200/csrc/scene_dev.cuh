@@ -81,6 +81,7 @@ struct DevScene {
   const double *tris;
   const float4 *tri32; // non-null: the nine vertex coordinates of every triangle as binary32 (exactly representable), three float4 per row
   const int32_t *tri_mat;
+  const double *tri_uv; // optional: per triangle {u0 v0 u1 v1 u2 v2} (b200rt_scene_desc::tri_uv)
   const b200rt_volume *volumes;
   const b200rt_material *materials;
   const b200rt_texture *textures;
@@ -104,6 +105,7 @@ struct DevScene {
   const Chain *chains;
   uint32_t n_entries;
   int32_t has_volumes;
+  const DevScene *self; // this structure again, in global memory (for out-of-line device functions)
   double bound[3]; // max |finite box plane| per axis over the whole BVH: sizes the fp32 error margin of the box test
 };
 

@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
   const PathBuf cur = pool_cur(c, P), nxt = pool_nxt(c, P);
   // survivors are appended to the other pool with ONE global atomic per CTA iteration (same-address atomics are the
   // scarce resource of this kernel family: see k_classify); double-buffered by iteration parity
-  __shared__ uint32_t s_cnt[2][4], s_base[2];
+  __shared__ uint32_t s_cnt[2][4], s_base[2], s_oct[2][8][4];
   const uint32_t n = c->q_count[KIND];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int par = 0;
@@ -89,15 +89,44 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
       }
     }
     const unsigned smask = __ballot_sync(0xffffffffu, survives);
-    if (lane == 0) s_cnt[par][warp] = (uint32_t)__popc(smask);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const uint32_t tot = s_cnt[par][0] + s_cnt[par][1] + s_cnt[par][2] + s_cnt[par][3];
-      s_base[par] = tot ? atomicAdd(&c->n_next, tot) : 0;
+    uint32_t pos;
+    if (wp.octant_sort) {
+      // The survivors of this CTA iteration (<= 128 neighbouring paths) are written grouped by the OCTANT of their new direction,
+      // so that the 32-ray batches the extend kernel hands to a warp walk the tree in a similar order.  No extra memory traffic:
+      // only the slot a path gets inside the CTA's block of the next pool changes.
+      const int oct = survives ? ((out_ray.d.x < 0 ? 1 : 0) | (out_ray.d.y < 0 ? 2 : 0) | (out_ray.d.z < 0 ? 4 : 0)) : 8;
+      uint32_t before = 0; // survivors of my warp in my octant on lower lanes
+#pragma unroll
+      for (int o = 0; o < 8; o++) {
+        const unsigned m = __ballot_sync(0xffffffffu, oct == o);
+        if (lane == 0) s_oct[par][o][warp] = (uint32_t)__popc(m);
+        if (oct == o) before = (uint32_t)__popc(m & ((1u << lane) - 1u));
+      }
+      __syncthreads();
+      if (warp == 0) { // exclusive scan over (octant major, warp minor): 32 counters, one per lane
+        const uint32_t v = s_oct[par][lane >> 2][lane & 3];
+        uint32_t incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+          if (lane >= d) incl += t;
+        }
+        s_oct[par][lane >> 2][lane & 3] = incl - v;
+        if (lane == 31) s_base[par] = incl ? atomicAdd(&c->n_next, incl) : 0;
+      }
+      __syncthreads();
+      pos = s_base[par] + (oct < 8 ? s_oct[par][oct][warp] : 0u) + before;
+    } else {
+      if (lane == 0) s_cnt[par][warp] = (uint32_t)__popc(smask);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        const uint32_t tot = s_cnt[par][0] + s_cnt[par][1] + s_cnt[par][2] + s_cnt[par][3];
+        s_base[par] = tot ? atomicAdd(&c->n_next, tot) : 0;
+      }
+      __syncthreads();
+      pos = s_base[par] + (uint32_t)__popc(smask & ((1u << lane) - 1u));
+      for (int w = 0; w < warp; w++) pos += s_cnt[par][w];
     }
-    __syncthreads();
-    uint32_t pos = s_base[par] + (uint32_t)__popc(smask & ((1u << lane) - 1u));
-    for (int w = 0; w < warp; w++) pos += s_cnt[par][w];
     if (survives) {
       store_path(nxt, pos, out_ray, T, pixel, sample, bounce, make_setup(wp.bound, out_ray));
     }

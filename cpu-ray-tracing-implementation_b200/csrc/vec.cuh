@@ -14,10 +14,13 @@
 
 #define HD __host__ __device__ __forceinline__
 #define DEV __device__ __forceinline__
-// cold paths (volumes, noise textures): called, not inlined, so that the hot traversal / shading loops stay small in the
-// instruction cache (ncu: stall_no_instruction was 24 % of the samples of the RTNW extend kernel with everything inlined)
+// Experiment (-DB200_COLD_NOINLINE=1): cold paths (volumes, noise textures) called instead of inlined, to shrink the hot loops'
+// instruction footprint (ncu: stall_no_instruction was 24 % of the samples of the RTNW extend kernel).  Measured on B200
+// (profiles/r02_g_builds.jsonl, r02_h_builds.jsonl): SLOWER on every scene, 2-9 %, whether the scene is passed by reference
+// (the kernel parameter gets a local-memory copy per thread) or through DevScene::self: an out-of-line call forces the ray
+// and the entry it takes by reference into local memory.  Off.
 #ifndef B200_COLD_NOINLINE
-#define B200_COLD_NOINLINE 1
+#define B200_COLD_NOINLINE 0
 #endif
 #if B200_COLD_NOINLINE
 #define DEV_COLD __device__ __noinline__

@@ -67,6 +67,7 @@ struct WaveParams {
   uint64_t seed;
   uint32_t npix, width;
   int32_t spp_begin, max_depth, kill_zero, refill; // refill: idle lanes per warp that trigger a fetch in k_extend_persistent
+  int32_t octant_sort; // k_shade: survivors of a CTA iteration are written grouped by the octant of their new direction
   int32_t leaf_lanes; // k_extend_persistent<UNI>: lanes waiting at a leaf that trigger the leaf phase (32 = only when no lane is at a node)
   int32_t fused_miss; // 1 = the scene has no background: a miss adds 0, the extend kernel finishes it itself (no miss queue, no miss launch)
   double bound[3]; // DevScene::bound, for the producers' make_setup

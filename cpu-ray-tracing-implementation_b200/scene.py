@@ -58,6 +58,7 @@ class Scene:
         self.light_index = -1
         self.background_tex = -1
         self.name = ""
+        self.tri_uv = np.zeros((0, 6))  # optional (ABI 2): per-triangle vertex texture coordinates, empty = the reference's behaviour
 
     # ---- construction -------------------------------------------------------------------------
     @classmethod
@@ -90,10 +91,14 @@ class Scene:
             setattr(s, name, _view(getattr(d, name), counts[name], dt, shape))
         for k in _SCALARS:
             setattr(s, k, int(getattr(d, k)))
+        if d.tri_uv:
+            s.tri_uv = _view(d.tri_uv, d.n_tris, np.dtype("<f8"), (6,))
         return s
 
     def save(self, path, **extra):
         payload = {name: getattr(self, name) for name, _, _ in _ARRAYS}
+        if len(self.tri_uv):
+            payload["tri_uv"] = self.tri_uv
         payload["scalars"] = np.array([getattr(self, k) for k in _SCALARS], dtype=np.int64)
         payload.update(extra)
         np.savez_compressed(path, **payload)
@@ -107,6 +112,8 @@ class Scene:
             setattr(s, name, np.ascontiguousarray(arr.astype(dt, copy=False)).reshape((-1,) + shape))
         for k, v in zip(_SCALARS, z["scalars"].tolist()):
             setattr(s, k, int(v))
+        if "tri_uv" in getattr(z, "files", []):
+            s.tri_uv = np.ascontiguousarray(z["tri_uv"], dtype="<f8").reshape(-1, 6)
         return s
 
     # ---- C ABI view -----------------------------------------------------------------------------
@@ -144,6 +151,11 @@ class Scene:
         d.light_kind = self.light_kind
         d.light_index = self.light_index
         d.background_tex = self.background_tex
+        if len(self.tri_uv):
+            if len(self.tri_uv) != len(self.tri_mat):
+                raise ValueError("tri_uv must have one row per triangle")
+            self.tri_uv = np.ascontiguousarray(self.tri_uv, dtype="<f8").reshape(-1, 6)
+            d.tri_uv = p("tri_uv")
         return d, keep
 
     # ---- summaries ------------------------------------------------------------------------------

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define B200RT_ABI_VERSION 1
+#define B200RT_ABI_VERSION 2 /* 2: b200rt_scene_desc::tri_uv, float images, B200RT_TEX_PICTURE_LINEAR */
 
 typedef enum b200rt_status {
   B200RT_OK = 0,
@@ -186,6 +186,9 @@ typedef struct b200rt_scene_desc {
   int32_t light_index;  /* row in quads / spheres */
   int32_t background_tex; /* camera::background_ (src/camera.h:329); -1 = nullptr */
   int32_t reserved;
+  const double *tri_uv; /* NULL (what the reference does: triangle::hit leaves rec.u, rec.v unwritten, src/triangle.h:35-39; the
+                           ABI reports 0) or n_tris x {u0 v0 u1 v1 u2 v2}: texture coordinates of the three vertices, interpolated
+                           with the barycentric weights of the hit (opt-in, SURVEY.md 8f rank 3: glTF TEXCOORD_0) */
 } b200rt_scene_desc;
 
 /* ------------------------------------------------------------------- camera
@@ -247,6 +250,8 @@ typedef enum b200rt_option {
                                   kernels declare as a persisting L2 access-policy window (the wave's path state streams past it) */
   B200RT_OPT_TRI_F32 = 20,     /* 1 (default): triangle vertices are kept as 48-byte binary32 rows when every coordinate is exactly representable
                                   (glTF positions are), and widened after the load: identical binary64 operands, 40 % fewer bytes per test */
+  B200RT_OPT_OCTANT_SORT = 21, /* tuning: 1 = the shade kernels write the surviving paths of a CTA iteration grouped by the octant of their new
+                                  direction (more coherent 32-ray batches for the extend kernel; same paths, same samples) */
   B200RT_OPT_REFILL_LANES = 5   /* idle lanes per warp at which the persistent extend kernel claims new rays (32 = fixed 32-ray batches; 0 (default) = 32, or 8 from 32 Ki BVH nodes) */
 } b200rt_option;
 

@@ -203,6 +203,11 @@ bool triangle_hit(const Scene &s, int row, const Ray &r, Interval iv, Rec &rec) 
   rec.mat = s.d->tri_mat[row];
   rec.u = 0; // not written by the reference (src/triangle.h:35-39); the ABI defines 0
   rec.v = 0;
+  if (s.d->tri_uv) { // the backend's opt-in (b200rt_scene_desc::tri_uv): vertex texture coordinates weighted with b0, b1
+    const double *w = s.d->tri_uv + (size_t)row * 6;
+    rec.u = (1 - b0 - b1) * w[0] + b0 * w[2] + b1 * w[4];
+    rec.v = (1 - b0 - b1) * w[1] + b0 * w[3] + b1 * w[5];
+  }
   return true;
 }
 

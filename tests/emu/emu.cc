@@ -47,6 +47,7 @@ void *emu_scene_create(const b200rt_scene_desc *d, int leaf_size) {
   S.chain_ops = e->fs.chain_ops.data(), S.chains = e->fs.chains.data(), S.n_entries = (uint32_t)e->ordered.size();
   S.has_volumes = e->fs.has_volumes;
   for (int k = 0; k < 3; k++) S.bound[k] = e->bvh.bound[k];
+  S.self = &e->S;
   return e;
 }
 void emu_scene_destroy(void *h) { delete static_cast<EmuScene *>(h); }

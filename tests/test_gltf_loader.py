@@ -91,3 +91,70 @@ def test_fox_triangles_equal_the_references_own_load():
     assert t.shape == ref.shape == (576, 9)
     key = lambda a: a[np.lexsort(a.T[::-1])]
     assert np.array_equal(key(t), key(ref))
+
+
+# ------------------------------------------------------------------------------------------------ materials, textures, uv
+FIXTURE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "aux", "textured.gltf")
+
+
+def textured_scene():
+    m = pkg.gltf.load_mesh(FIXTURE)
+    return m, pkg.gltf.mesh_scene(m, light=((-1, 6, -3), (3, 0, 0), (0, 0, 3), (8, 8, 8)), background_rgb=(0.2, 0.2, 0.3))
+
+
+def test_load_mesh_reads_what_the_reference_drops():
+    """TEXCOORD_0, per-primitive materials, the base-colour texture, u8 / u16 / u32 indices and the node transform
+    (src/gltf_loader.h:65 `// Material material;`, :312 `// loadMaterials();`, :295-303; src/main.cc:367-375)."""
+    m, s = textured_scene()
+    assert m["triangles"].shape == (60, 9) and m["uv"].shape == (60, 6)
+    assert np.bincount(m["material"]).tolist() == [32, 8, 2, 18]  # 4x4, 2x2, 1x1 and 3x3 grids of quads
+    assert m["images"][0].shape == (8, 8, 3) and m["images"][0].dtype == np.uint8
+    # the node's scale 1.5 and translation (0.5, 1, -2) are applied: the first grid spans x in [-3, -1] * 1.5 + 0.5
+    x = m["triangles"][:32].reshape(-1, 3)[:, 0]
+    assert np.isclose(x.min(), -4.0) and np.isclose(x.max(), -1.0)
+    kinds = s.materials["kind"].tolist()
+    assert kinds[:4] == [abi.MAT_LAMBERTIAN, abi.MAT_METAL, abi.MAT_DIFFUSE_LIGHT, abi.MAT_DIELECTRIC]
+    assert s.textures["kind"][0] == abi.TEX_PICTURE and np.isclose(s.materials["p0"][1], 0.25) and np.isclose(s.materials["p0"][3], 1.45)
+    assert np.allclose(s.textures["c0"][2], [6.0, 5.4, 4.8])
+    # the reference's own behaviour stays available: positions only, file order, no transform
+    ref = pkg.gltf.load_triangles(FIXTURE, mode="reference")
+    assert len(ref) == 32 + 18  # only the u16-indexed primitives (src/main.cc:368)
+    # linearised 8-bit texels, as stbi_loadf + image::convert_to_bytes would hold them
+    assert m["images"][0][0, 0].tolist() == [255, 0, 0] and m["images"][0][7, 7].tolist() == [0, 0, 255]
+
+
+def test_triangle_uv_interpolation_in_the_oracle(build_oracle):
+    """b200rt_scene_desc::tri_uv: u, v of a triangle hit = the vertex coordinates weighted with the hit's barycentrics; without
+    tri_uv the record carries 0, 0 as the reference leaves it (src/triangle.h:35-39)."""
+    m, s = textured_scene()
+    rng = np.random.RandomState(2)
+    k = rng.randint(0, 60, 800)
+    b = rng.dirichlet([1, 1, 1], 800)
+    T = m["triangles"].astype(np.float64).reshape(-1, 3, 3)
+    target = (b[:, :, None] * T[k]).sum(axis=1)
+    rays = np.zeros((800, 7))
+    rays[:, 0:3] = target + [0.1, 0.2, 5.0]
+    rays[:, 3:6] = target - rays[:, 0:3]
+    out = build_oracle.trace(s, rays)
+    hit = out["prim"] >= 0
+    assert hit.mean() > 0.95
+    # which triangle was hit: nearest along the ray may be another layer; recompute the expectation from the hit point
+    uv = s.tri_uv.reshape(-1, 3, 2)
+    P = out["p"][hit]
+    ok = 0
+    for p, got in zip(P, out["uv"][hit]):
+        for t in range(60):  # find a triangle containing p
+            a, bb, c = T[t]
+            n = np.cross(bb - a, c - a)
+            if abs(np.dot(p - a, n)) > 1e-9 * np.linalg.norm(n):
+                continue
+            w1 = np.dot(np.cross(p - a, c - a), n) / np.dot(n, n)
+            w2 = np.dot(np.cross(bb - a, p - a), n) / np.dot(n, n)
+            if w1 >= -1e-9 and w2 >= -1e-9 and w1 + w2 <= 1 + 1e-9:
+                want = (1 - w1 - w2) * uv[t, 0] + w1 * uv[t, 1] + w2 * uv[t, 2]
+                if np.allclose(got, want, atol=1e-9):
+                    ok += 1
+                    break
+    assert ok >= 0.99 * hit.sum(), (ok, hit.sum())
+    s.tri_uv = np.zeros((0, 6))
+    assert not build_oracle.trace(s, rays)["uv"].any()

@@ -162,6 +162,25 @@ CONVERGED = {"cornell": (24, 1_500_000), "rtow": (24, 300_000), "rtnw": (16, 1_6
 SPONZA_SMALL = 16384  # triangles of the stand-in mesh used for the converged render: the reference's x-sorted tree needs 0.3 ms per ray on the full one
 
 
+def append_converged(name, extra_spp):
+    """More reference samples for an existing converged_<name>.npz (independent stream), summed into it."""
+    path = os.path.join(OUT, "aux", f"converged_{name}.npz")
+    z = dict(np.load(path))
+    width = CONVERGED[name][0]
+    rs = R.RefScene(name, width=width)
+    assert rs.camera.to_bytes() == z["cam"].tobytes()
+    s, q, st = rs.render(extra_spp, seed=20261105 + int(z["ref_spp"]), threads=0, rng_mode=1)
+    z["ref_sum"], z["ref_sumsq"] = z["ref_sum"] + s, z["ref_sumsq"] + q
+    z["ref_spp"] = np.int64(int(z["ref_spp"]) + extra_spp)
+    z["ref_rays_count"] = np.int64(int(z["ref_rays_count"]) + st["rays"])
+    z["ref_nan_samples"] = np.int64(int(z["ref_nan_samples"]) + st["nan_samples"])
+    np.savez_compressed(path, **z)
+    n = int(z["ref_spp"])
+    m = z["ref_sum"] / n
+    var = np.maximum(z["ref_sumsq"] / n - m * m, 0)
+    print(f"converged {name}: now {n} spp; per-channel noise floor {np.sqrt(var.mean(axis=(0, 1)) / n)}", flush=True)
+
+
 def make_converged(name):
     """tests/golden/aux/converged_<name>.npz: the reference's OWN high-spp render (its generate_ray + ray_color on all host threads)
     of a BASELINE.json config at thumbnail resolution: per-pixel sum and sum of squares.  The GPU test renders the same
@@ -192,6 +211,10 @@ def make_converged(name):
 
 
 if __name__ == "__main__":
+    if "--append-converged" in sys.argv:
+        a = [x for x in sys.argv[1:] if not x.startswith("--")]
+        append_converged(a[0], int(a[1]))
+        sys.exit(0)
     if "--converged" in sys.argv:
         for n in ([a for a in sys.argv[1:] if not a.startswith("--")] or CONVERGED):
             make_converged(n)
