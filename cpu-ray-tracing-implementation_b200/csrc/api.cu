@@ -112,6 +112,9 @@ struct b200rt_ctx {
     Rec *recs = nullptr;
     Queues queues{};
     WaveCtl *ctl = nullptr;
+    uint32_t *sort_keys[2] = {nullptr, nullptr}, *sort_vals[2] = {nullptr, nullptr}; // B200RT_OPT_RAY_SORT (experiment)
+    void *sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0;
     WaveCtl *h_ctl = nullptr; // pinned
     cudaStream_t stream = nullptr; // pipeline stream (two-pipeline mode)
     cudaEvent_t done = nullptr;
@@ -130,9 +133,10 @@ struct b200rt_ctx {
   } w[B200_MAX_PIPELINES];
   cudaStream_t cap_stream = nullptr; // stream captures are recorded on (never executes anything)
   int l2_persist = 1;  // B200RT_OPT_L2_PERSIST
-  int tri_f32 = 1;     // B200RT_OPT_TRI_F32
+  int tri_f32 = 2;     // B200RT_OPT_TRI_F32: 0 = binary64 rows, 2 = binary32 rows (default), 1 = binary32 rows repeated in leaf order (measured: no gain)
   size_t hot_bytes = 0; // prefix of the scene arena that the traversal reads per node / leaf
   size_t l2_window_max = 0, l2_persist_max = 0;
+  int ray_sort = 0;    // B200RT_OPT_RAY_SORT
   int octant_sort = 0; // B200RT_OPT_OCTANT_SORT
   int extend_loop = 0; // B200RT_OPT_EXTEND_LOOP: 0 = while-while, 1 = warp-uniform threshold if-if
   int leaf_lanes = 8;  // B200RT_OPT_LEAF_LANES
@@ -399,7 +403,15 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     c->carveout_pct = (int)value;
     return B200RT_OK;
   case B200RT_OPT_L2_PERSIST: c->l2_persist = value != 0; return B200RT_OK;
-  case B200RT_OPT_TRI_F32: c->tri_f32 = value != 0; return B200RT_OK; // takes effect at the next b200rt_upload_scene
+  case B200RT_OPT_TRI_F32:
+    if (value != 0 && value != 1 && value != 2) return fail(B200RT_ERR_INVALID, "triangle rows: 0 (binary64), 1 (binary32, also in leaf order) or 2 (binary32)");
+    c->tri_f32 = (int)value; // takes effect at the next b200rt_upload_scene
+    return B200RT_OK; // takes effect at the next b200rt_upload_scene
+  case B200RT_OPT_RAY_SORT:
+    if (!(value >= 0 && value <= 7)) return fail(B200RT_ERR_INVALID, "ray sort mode must be in [0, 7]");
+    c->ray_sort = (int)value;
+    for (auto &w : c->w) w.capacity = 0; // the sort buffers are allocated with the wave pools
+    return B200RT_OK;
   case B200RT_OPT_OCTANT_SORT: c->octant_sort = value != 0; return B200RT_OK;
   case B200RT_OPT_EXTEND_LOOP:
     if (value != 0 && value != 1) return fail(B200RT_ERR_INVALID, "extend loop must be 0 (while-while) or 1 (warp-uniform)");
@@ -507,7 +519,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
     auto pad = [](size_t n) { return ((n ? n : 16) + 255) & ~(size_t)255; };
     size_t total = 0;
     total += pad(wide.size() * sizeof(BvhNode4)) + pad(bvh.nodes.size() * sizeof(BvhNode)) + pad(ordered.size() * sizeof(Entry)) + pad(ordered.size());
-    total += pad(tri32.size() * 4) + pad((size_t)d->n_tris * B200RT_TRI_STRIDE * 8) + pad((size_t)d->n_spheres * B200RT_SPHERE_STRIDE * 8) + pad((size_t)d->n_quads * B200RT_QUAD_STRIDE * 8);
+    total += 2 * pad(tri32.size() * 4) + pad(ordered.size() * 48) + pad((size_t)d->n_tris * B200RT_TRI_STRIDE * 8) + pad((size_t)d->n_spheres * B200RT_SPHERE_STRIDE * 8) + pad((size_t)d->n_quads * B200RT_QUAD_STRIDE * 8);
     total += pad(fs.chain_ops.size() * sizeof(ChainOp)) + pad(fs.chains.size() * sizeof(Chain)) + pad(fs.vol_inst.size() * sizeof(VolInst)) + pad(fs.bentries.size() * sizeof(Entry));
     total += pad((size_t)d->n_spheres * 4) + pad((size_t)d->n_quads * 4) + pad((size_t)d->n_tris * 4) + pad(d->n_volumes * sizeof(b200rt_volume));
     total += pad(d->n_materials * sizeof(b200rt_material)) + pad(d->n_textures * sizeof(b200rt_texture));
@@ -521,10 +533,14 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
       UP(bvh.nodes.data(), bvh.nodes.size(), &S.bvh, "bvh");
     UP(ordered.data(), ordered.size(), &S.entries, "entries");
   }
-  if (!tri32.empty()) {
-    const float *p32 = nullptr;
-    UP(tri32.data(), tri32.size(), &p32, "tri32");
-    S.tri32 = reinterpret_cast<const float4 *>(p32);
+  std::vector<float> tri32e; // the binary32 rows in leaf (entry) order: a leaf test fetches entry and vertices in parallel
+  if (!tri32.empty() && !use_device_builder && c->tri_f32 == 1) {
+    tri32e.assign(ordered.size() * 12, 0.0f);
+    for (size_t k = 0; k < ordered.size(); k++)
+      if (entry_kind(ordered[k]) == E_TRI) std::memcpy(&tri32e[k * 12], &tri32[(size_t)ordered[k].row * 12], 48);
+    const float *pe = nullptr;
+    UP(tri32e.data(), tri32e.size(), &pe, "tri32e");
+    S.tri32e = reinterpret_cast<const float4 *>(pe);
   }
   UP(d->spheres, (size_t)d->n_spheres * B200RT_SPHERE_STRIDE, &S.spheres, "spheres");
   UP(d->quads, (size_t)d->n_quads * B200RT_QUAD_STRIDE, &S.quads, "quads");
@@ -537,6 +553,11 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
     cudaGetLastError();
   }
   // ---- warm: read per finished ray / per shaded hit
+  if (!tri32.empty()) { // row order: volume boundaries, the mirror traversal
+    const float *p32 = nullptr;
+    UP(tri32.data(), tri32.size(), &p32, "tri32");
+    S.tri32 = reinterpret_cast<const float4 *>(p32);
+  }
   if (!tri32.empty()) UP(d->tris, (size_t)d->n_tris * B200RT_TRI_STRIDE, &S.tris, "tris"); // normals for finish_hit
   UP(d->sphere_mat, d->n_spheres, &S.sphere_mat, "sphere_mat");
   UP(d->quad_mat, d->n_quads, &S.quad_mat, "quad_mat");
@@ -762,8 +783,8 @@ int b200rt_generate_rays(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
 
 namespace {
 
-int ensure_wave(b200rt_ctx::WaveSet &w, uint32_t capacity, bool mirror) {
-  if (w.capacity >= capacity && (!mirror || w.mirror)) return B200RT_OK;
+int ensure_wave(b200rt_ctx::WaveSet &w, uint32_t capacity, bool mirror, bool sort = false) {
+  if (w.capacity >= capacity && (!mirror || w.mirror) && (!sort || w.sort_tmp)) return B200RT_OK;
   w.drop_graph(); // its kernel nodes point into the pools that are about to be freed
   w.mem.release();
   w.capacity = 0;
@@ -777,6 +798,16 @@ int ensure_wave(b200rt_ctx::WaveSet &w, uint32_t capacity, bool mirror) {
   if (mirror) CU(col((void **)&w.recs, sizeof(Rec)));
   for (int k = 0; k < B200_NQUEUES; k++) CU(col((void **)&w.queues.q[k], 4));
   CU(w.mem.alloc((void **)&w.ctl, sizeof(WaveCtl)));
+  w.sort_tmp = nullptr;
+  if (sort) {
+    for (int k = 0; k < 2; k++) {
+      CU(col((void **)&w.sort_keys[k], 4));
+      CU(col((void **)&w.sort_vals[k], 4));
+    }
+    w.sort_tmp_bytes = 0;
+    CU(cub::DeviceRadixSort::SortPairs(nullptr, w.sort_tmp_bytes, w.sort_keys[0], w.sort_keys[1], w.sort_vals[0], w.sort_vals[1], (int)capacity, 0, 21));
+    CU(w.mem.alloc(&w.sort_tmp, w.sort_tmp_bytes));
+  }
   w.capacity = capacity;
   w.mirror = mirror;
   return B200RT_OK;
@@ -788,7 +819,7 @@ template <class K>
 void launch_extend(K kernel, b200rt_ctx *c, b200rt_ctx::WaveSet &w, int ctas_per_sm, int threads, int smem_per_cta, cudaStream_t s, const Pools &cur, const WaveParams &wp) {
   const int want_kb = (ctas_per_sm * (smem_per_cta + 1024) + 1023) / 1024;
   cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, c->carveout_pct >= 0 ? c->carveout_pct : std::min(100, (want_kb * 100 + 227) / 228));
-  kernel<<<c->sm_count * ctas_per_sm, threads, 0, s>>>(w.ctl, c->S, cur, w.hits, wp);
+  kernel<<<c->sm_count * ctas_per_sm, threads, 0, s>>>(w.ctl, c->S, cur, w.hits, wp, (const uint32_t *)(c->ray_sort ? w.sort_vals[1] : nullptr));
 }
 
 template <bool MIRROR>
@@ -833,6 +864,10 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, const Dev
   }
   const bool tail = !mirror && c->tail_paths > 0;
   if (tail) k_tail<<<(int)((c->tail_paths + 63) / 64), 64, 0, s>>>(w.ctl, c->S, cur, d_rgb_sum, wp, c->tail_paths);
+  if (c->ray_sort && !mirror) { // experiment: a full radix sort per wave (its cost is not the point: the extend time after it is)
+    k_sort_keys<<<g_gen, 256, 0, s>>>(w.ctl, cur, wp, c->ray_sort, w.sort_keys[0], w.sort_vals[0], w.capacity);
+    CU(cub::DeviceRadixSort::SortPairs(w.sort_tmp, w.sort_tmp_bytes, w.sort_keys[0], w.sort_keys[1], w.sort_vals[0], w.sort_vals[1], (int)w.capacity, 0, 21, s));
+  }
   if (ext_events) {
     cudaEvent_t a, b; // owned by the caller's guard from the moment they exist
     CU(cudaEventCreate(&a));
@@ -844,7 +879,7 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, const Dev
   if (mirror)
     k_extend<true><<<g_ext, 128, 0, s>>>(w.ctl, c->S, cur, w.hits, w.recs, w.queues, wp);
   else
-    switch (c->extend_blocks * 2 + (c->speculative ? 1 : 0)) {
+    switch (c->S.bvh4 ? 0 : c->extend_blocks * 2 + (c->speculative ? 1 : 0)) { // the tuning variants below walk the BVH2 only
     // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
 #define EXT(MAXREG, SPEC, WARPS, STAGES)                                                                               \
   launch_extend(k_extend_persistent<MAXREG, SPEC, WARPS, STAGES, false>, c, w, 65536 / (MAXREG * WARPS * 32), WARPS * 32, WARPS * STAGES * 3584, s, cur, wp)
@@ -1006,7 +1041,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     tot[p] = (unsigned long long)npix * (unsigned long long)(hi - lo);
     uint32_t capacity = c->wave_paths / (uint32_t)n_pipe;
     if (tot[p] < capacity) capacity = (uint32_t)((tot[p] + 31) & ~31ull);
-    if ((rc = ensure_wave(c->w[p], capacity, mirror)) != B200RT_OK) return rc;
+    if ((rc = ensure_wave(c->w[p], capacity, mirror, c->ray_sort != 0 && !mirror)) != B200RT_OK) return rc;
     capacity = c->w[p].capacity; // a larger pool from an earlier call is kept; use min(wave_paths share, pool)
     if (capacity > c->wave_paths / (uint32_t)n_pipe) capacity = c->wave_paths / (uint32_t)n_pipe;
     cap[p] = capacity;
@@ -1065,7 +1100,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     for (int p = 0; p < n_pipe; p++) {
       std::string key;
       key_add(key, c->S), key_add(key, cam), key_add(key, wp[p]), key_add(key, cap[p]), key_add(key, d_rgb_sum), key_add(key, ext_ctas);
-      key_add(key, c->tail_paths), key_add(key, c->extend_blocks), key_add(key, c->speculative), key_add(key, c->extend_stages), key_add(key, c->carveout_pct), key_add(key, c->extend_loop), key_add(key, c->l2_persist);
+      key_add(key, c->tail_paths), key_add(key, c->extend_blocks), key_add(key, c->speculative), key_add(key, c->extend_stages), key_add(key, c->carveout_pct), key_add(key, c->extend_loop), key_add(key, c->l2_persist), key_add(key, c->ray_sort);
       key_add(key, c->kinds_present), key_add(key, c->w[p].pools), key_add(key, c->w[p].hits);
       if ((rc = ensure_wave_graph(c, c->w[p], key, cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas)) != B200RT_OK) return rc;
       CU(cudaGraphLaunch(c->w[p].graph_exec, ps[p]));

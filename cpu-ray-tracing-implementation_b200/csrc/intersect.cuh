@@ -16,41 +16,51 @@ namespace b200 {
 DEV bool contains(double lo, double hi, double x) { return lo <= x && x <= hi; } // src/interval.h:14
 
 // ---------------------------------------------------------------- transform chains
-DEV void rot_fwd(V &a, int i0, int i1, double s, double c) {
-  const double p0 = getc(a, i0), p1 = getc(a, i1);
-  setc(a, i0, c * p0 - s * p1);
-  setc(a, i1, s * p0 + c * p1);
-}
-DEV void rot_back(V &a, int i0, int i1, double s, double c) {
-  const double p0 = getc(a, i0), p1 = getc(a, i1);
-  setc(a, i0, c * p0 + s * p1);
-  setc(a, i1, -s * p0 + c * p1);
-}
-DEV void rot_axes(int kind, int &i0, int &i1) {
+// rotate_x / rotate_y / rotate_z act on the coordinate pairs (y,z) / (x,z) / (x,y) (src/hittable.h:125-149, 192-216, 259-284).
+// Written per axis with named components: indexing a V by a run-time axis number expands into select chains that made
+// the transform code 10 000 of the extend kernel's 23 000 instructions (nvdisasm line table, profiles/r02_m_codesize.txt).
+DEV void rot_fwd(int kind, V &a, double s, double c) {
   if (kind == B200RT_NODE_ROTATE_X) {
-    i0 = 1;
-    i1 = 2;
+    const double p0 = a.y, p1 = a.z;
+    a.y = c * p0 - s * p1;
+    a.z = s * p0 + c * p1;
   } else if (kind == B200RT_NODE_ROTATE_Y) {
-    i0 = 0;
-    i1 = 2;
+    const double p0 = a.x, p1 = a.z;
+    a.x = c * p0 - s * p1;
+    a.z = s * p0 + c * p1;
   } else {
-    i0 = 0;
-    i1 = 1;
+    const double p0 = a.x, p1 = a.y;
+    a.x = c * p0 - s * p1;
+    a.y = s * p0 + c * p1;
+  }
+}
+DEV void rot_back(int kind, V &a, double s, double c) {
+  if (kind == B200RT_NODE_ROTATE_X) {
+    const double p0 = a.y, p1 = a.z;
+    a.y = c * p0 + s * p1;
+    a.z = -s * p0 + c * p1;
+  } else if (kind == B200RT_NODE_ROTATE_Y) {
+    const double p0 = a.x, p1 = a.z;
+    a.x = c * p0 + s * p1;
+    a.z = -s * p0 + c * p1;
+  } else {
+    const double p0 = a.x, p1 = a.y;
+    a.x = c * p0 + s * p1;
+    a.y = -s * p0 + c * p1;
   }
 }
 // world ray -> object ray, outermost transform first
 DEV Ray chain_apply(const DevScene &S, int chain, Ray r) {
   if (chain == 0) return r;
   const Chain ch = S.chains[chain];
+#pragma unroll 1
   for (int k = 0; k < ch.count; k++) {
     const ChainOp op = S.chain_ops[ch.first + k];
     if (op.kind == B200RT_NODE_TRANSLATE) {
       r.o = r.o - v3(op.f0, op.f1, op.f2);
     } else {
-      int i0, i1;
-      rot_axes(op.kind, i0, i1);
-      rot_fwd(r.o, i0, i1, op.f0, op.f1);
-      rot_fwd(r.d, i0, i1, op.f0, op.f1);
+      rot_fwd(op.kind, r.o, op.f0, op.f1);
+      rot_fwd(op.kind, r.d, op.f0, op.f1);
     }
   }
   return r;
@@ -59,15 +69,14 @@ DEV Ray chain_apply(const DevScene &S, int chain, Ray r) {
 DEV void chain_unapply(const DevScene &S, int chain, V &p, V &n) {
   if (chain == 0) return;
   const Chain ch = S.chains[chain];
+#pragma unroll 1
   for (int k = ch.count - 1; k >= 0; k--) {
     const ChainOp op = S.chain_ops[ch.first + k];
     if (op.kind == B200RT_NODE_TRANSLATE) {
       p = p + v3(op.f0, op.f1, op.f2);
     } else {
-      int i0, i1;
-      rot_axes(op.kind, i0, i1);
-      rot_back(p, i0, i1, op.f0, op.f1);
-      rot_back(n, i0, i1, op.f0, op.f1);
+      rot_back(op.kind, p, op.f0, op.f1);
+      rot_back(op.kind, n, op.f0, op.f1);
     }
   }
 }
@@ -168,12 +177,16 @@ DEV bool quad_row_t(const DevScene &S, int row, const Ray &r, double lo, double 
 }
 
 // ---------------------------------------------------------------- triangle
+DEV bool tri_core_t(const V &p0, const V &p1, const V &p2, const Ray &r, double lo, double hi, double &t);
+DEV void tri32_unpack(const float4 &a, const float4 &b, const float4 &c, V &p0, V &p1, V &p2) {
+  p0 = v3((double)a.x, (double)a.y, (double)a.z), p1 = v3((double)a.w, (double)b.x, (double)b.y), p2 = v3((double)b.z, (double)b.w, (double)c.x);
+}
 DEV bool tri_row_t(const DevScene &S, int row, const Ray &r, double lo, double hi, double &t) {
   V p0, p1, p2;
   if (S.tri32) { // 48-byte binary32 row, widened: the same binary64 operands as the 96-byte row holds (checked at upload)
     const float4 *q = S.tri32 + (size_t)row * 3;
     const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
-    p0 = v3((double)a.x, (double)a.y, (double)a.z), p1 = v3((double)a.w, (double)b.x, (double)b.y), p2 = v3((double)b.z, (double)b.w, (double)c.x);
+    tri32_unpack(a, b, c, p0, p1, p2);
   } else {
     const double *q = S.tris + (size_t)row * B200RT_TRI_STRIDE;
     double a0, a1, a2, b0_, b1_, b2_, c0, c1, c2, nx;
@@ -184,6 +197,9 @@ DEV bool tri_row_t(const DevScene &S, int row, const Ray &r, double lo, double h
     ld2(q + 8, c2, nx);
     p0 = v3(a0, a1, a2), p1 = v3(b0_, b1_, b2_), p2 = v3(c0, c1, c2);
   }
+  return tri_core_t(p0, p1, p2, r, lo, hi, t);
+}
+DEV bool tri_core_t(const V &p0, const V &p1, const V &p2, const Ray &r, double lo, double hi, double &t) {
   const V e1 = p1 - p0, e2 = p2 - p0, sv = r.o - p0;
   const V s1 = cross(r.d, e2), s2 = cross(sv, e1);
   const double det = dot(s1, e1);
@@ -243,9 +259,15 @@ DEV bool boundary_t(const DevScene &S, const VolInst &vi, const Ray &r, double l
 DEV_COLD bool volume_t(const DevScene *Sp, const Entry &e, const Ray &r, double lo, double hi, const Stream &st, int bounce, double &t) {
   const DevScene &S = *Sp;
   const VolInst vi = S.vol_inst[e.row];
-  double t1, t2;
-  if (!boundary_t(S, vi, r, -B200_INF, B200_INF, t1)) return false;
-  if (!boundary_t(S, vi, r, t1 + 0.0001, B200_INF, t2)) return false;
+  // the two boundary queries of src/volumne.h:21-24 (universe, then t1 + 0.0001 .. infinity) as ONE call site in a loop:
+  // boundary_t carries every primitive test, and the extend kernel is sensitive to its instruction footprint
+  double tb[2], from = -B200_INF;
+#pragma unroll 1
+  for (int k = 0; k < 2; k++) {
+    if (!boundary_t(S, vi, r, from, B200_INF, tb[k])) return false;
+    from = tb[0] + 0.0001;
+  }
+  double t1 = tb[0], t2 = tb[1];
   if (t1 < lo) t1 = lo;
   if (t2 > hi) t2 = hi;
   if (t1 >= t2) return false;
@@ -263,7 +285,8 @@ DEV_COLD bool volume_t(const DevScene *Sp, const Entry &e, const Ray &r, double 
 #define B200_SPHERE_FASTPATH 0
 #endif
 // ---------------------------------------------------------------- one leaf entry: accepted t in [lo, hi]
-DEV bool entry_t(const DevScene &S, const Entry &e, const Ray &rw, double lo, double hi, const Stream &st, int bounce, double &t) {
+// pos = the entry's position in DevScene::entries (the BVH leaf order), or -1 when it is not one of those
+DEV bool entry_t(const DevScene &S, const Entry &e, int pos, const Ray &rw, double lo, double hi, const Stream &st, int bounce, double &t) {
   const int kind = entry_kind(e);
 #if B200_SPHERE_FASTPATH
   if (e.kind_chain == (uint32_t)E_SPHERE) return sphere_row_t(S, e.row, false, rw, lo, hi, t); // hot path: untransformed static sphere
@@ -274,7 +297,15 @@ DEV bool entry_t(const DevScene &S, const Entry &e, const Ray &rw, double lo, do
   case E_SPHERE:
   case E_SPHERE_MOVING: return sphere_row_t(S, e.row, kind == E_SPHERE_MOVING, r, lo, hi, t); // one inlined copy for both
   case E_QUAD: return quad_row_t(S, e.row, r, lo, hi, t, a, b);
-  case E_TRI: return tri_row_t(S, e.row, r, lo, hi, t) && t == t; // a NaN t is a "hit" in the reference; only the mirror traversal reproduces that
+  case E_TRI: { // a NaN t is a "hit" in the reference; only the mirror traversal reproduces that
+    if (S.tri32e && pos >= 0) { // vertices stored by entry position: their address does not wait for the entry's own load
+      const float4 *q = S.tri32e + (size_t)pos * 3;
+      V p0, p1, p2;
+      tri32_unpack(__ldg(q), __ldg(q + 1), __ldg(q + 2), p0, p1, p2);
+      return tri_core_t(p0, p1, p2, r, lo, hi, t) && t == t;
+    }
+    return tri_row_t(S, e.row, r, lo, hi, t) && t == t;
+  }
   case E_VOLUME: return volume_t(S.self, e, r, lo, hi, st, bounce, t);
   }
   return false;

@@ -122,14 +122,12 @@ __device__ __noinline__ bool mirror_hit(const MirrorCtx &cx, int idx, const Ray 
   case B200RT_NODE_ROTATE_X:
   case B200RT_NODE_ROTATE_Y:
   case B200RT_NODE_ROTATE_Z: {
-    int i0, i1;
-    rot_axes(n.kind, i0, i1);
     Ray rr = r;
-    rot_fwd(rr.o, i0, i1, n.f[0], n.f[1]);
-    rot_fwd(rr.d, i0, i1, n.f[0], n.f[1]);
+    rot_fwd(n.kind, rr.o, n.f[0], n.f[1]);
+    rot_fwd(n.kind, rr.d, n.f[0], n.f[1]);
     if (!mirror_hit(cx, n.a, rr, lo, hi, rec, visit)) return false;
-    rot_back(rec.p, i0, i1, n.f[0], n.f[1]);
-    rot_back(rec.normal, i0, i1, n.f[0], n.f[1]);
+    rot_back(n.kind, rec.p, n.f[0], n.f[1]);
+    rot_back(n.kind, rec.normal, n.f[0], n.f[1]);
     return true;
   }
   default: return mirror_leaf(cx, n, r, lo, hi, rec, visit);

@@ -85,17 +85,19 @@ DEV RaySetup make_setup(const double *bound, const Ray &r) {
   return s;
 }
 
-// Conservative entry / exit parameters of one box for the interval [lo, hi] (already rounded outward to fp32).
+// Conservative entry / exit parameters of one box for the interval [lo, hi] (already rounded outward to fp32): the box may be
+// hit iff  tn <= tf.  tn is the plain maximum of the near planes and lo; ALL the relative slack for the FFMAs' own rounding sits
+// on tf = f (1 + 1e-6).  That is enough because tn >= lo > 0 always (lo = 0.001 tsc rounded down): for f >= 0 the former
+// two-sided test  n (1 - 2^-21) <= f (1 + 2^-21)  is implied by  n <= f (1 + 2^-20 + ...) <= f (1 + 1e-6), and for f < 0 both
+// reject.  One FFMA per box instead of two and no |.| (r02: 2 of ~60 instructions per node step).
 DEV void slab32(float x0, float x1, float y0, float y1, float z0, float z1, const RaySetup &s, float lo, float hi, float &tn, float &tf) {
   const float ax = __fmaf_rn(x0, s.ix, -s.c0x), bx = __fmaf_rn(x1, s.ix, -s.c1x);
   const float ay = __fmaf_rn(y0, s.iy, -s.c0y), by = __fmaf_rn(y1, s.iy, -s.c1y);
   const float az = __fmaf_rn(z0, s.iz, -s.c0z), bz = __fmaf_rn(z1, s.iz, -s.c1z);
   // fminf / fmaxf drop NaNs (inf * 0 on an infinite plane): such an axis does not constrain the interval
-  const float n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), lo));
+  tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), lo));
   const float f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), hi));
-  const float K = 4.76837158203125e-7f; // 2^-21: the FFMA's own rounding, relative
-  tn = __fmaf_rn(-K, fabsf(n), n);
-  tf = __fmaf_rn(K, fabsf(f), f);
+  tf = __fmaf_rn(f, 1.0e-6f, f);
 }
 
 DEV void leaf_test(const DevScene &S, int32_t ref, const Ray &r, double lo, double hi, const Stream &st, int bounce, Best &best) {
@@ -107,7 +109,7 @@ DEV void leaf_test(const DevScene &S, int32_t ref, const Ray &r, double lo, doub
     e.kind_chain = (uint32_t)raw.x, e.row = raw.y, e.prim = raw.z, e.order = (uint32_t)raw.w;
     double t;
     // like the reference, later leaves see the interval shrunk to the best t so far (closed: ties get through)
-    if (entry_t(S, e, r, lo, best.entry < 0 ? hi : best.t, st, bounce, t)) {
+    if (entry_t(S, e, (int)(first + k), r, lo, best.entry < 0 ? hi : best.t, st, bounce, t)) {
       if (best.entry < 0 || t < best.t || (t == best.t && e.order > best.order)) {
         best.t = t;
         best.entry = (int32_t)(first + k);
@@ -131,7 +133,8 @@ DEV void prefetch_ref(const DevScene &S, int32_t ref, bool wide) {
 #endif
 }
 
-// One inner node: test both children, return the nearer accepted child (or B200_DONE) and push the other.
+// One inner node: test both children, return the nearer accepted child (or B200_DONE) and push the other.  Written without
+// control flow (selects and one predicated store) so that the node loop carries no reconvergence barriers.
 DEV int32_t node_step(const DevScene &S, int32_t cur, const RaySetup &rs, float lo32, float hi32, int32_t *stack, int &sp) {
   const float4 *q = reinterpret_cast<const float4 *>(S.bvh + cur);
   const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
@@ -139,15 +142,14 @@ DEV int32_t node_step(const DevScene &S, int32_t cur, const RaySetup &rs, float 
   float ln, lf, rn, rf;
   slab32(a.x, a.y, a.z, a.w, b.x, b.y, rs, lo32, hi32, ln, lf);
   slab32(b.z, b.w, c.x, c.y, c.z, c.w, rs, lo32, hi32, rn, rf);
-  const bool hl = ln <= lf, hr = rn <= rf;
-  if (hl && hr) {
-    const bool left_first = ln <= rn;
-    const int32_t far_ref = left_first ? ch.y : ch.x;
-    if (sp < B200_STACK) stack[sp++] = far_ref;
+  const bool hl = ln <= lf, hr = rn <= rf, both = hl && hr;
+  const bool left_first = ln <= rn;
+  const int32_t near_ref = left_first ? ch.x : ch.y, far_ref = left_first ? ch.y : ch.x;
+  if (both) { // cannot overflow: b200rt_upload_scene rejects trees deeper than B200_STACK (one push per level)
+    stack[sp++] = far_ref;
     prefetch_ref(S, far_ref, false);
-    return left_first ? ch.x : ch.y;
   }
-  return hl ? ch.x : (hr ? ch.y : B200_DONE);
+  return both ? near_ref : (hl ? ch.x : (hr ? ch.y : B200_DONE));
 }
 
 // One BVH4 node: test up to four children, return the nearest accepted one (or B200_DONE) and push the others, farthest
@@ -178,9 +180,10 @@ DEV int32_t node_step4(const DevScene &S, int32_t cur, const RaySetup &rs, float
   cswap4(k0, c0, k2, c2);
   cswap4(k1, c1, k3, c3);
   cswap4(k1, c1, k2, c2);
-  if (k3 < INF32 && sp < B200_STACK) stack[sp++] = c3, prefetch_ref(S, c3, true);
-  if (k2 < INF32 && sp < B200_STACK) stack[sp++] = c2, prefetch_ref(S, c2, true);
-  if (k1 < INF32 && sp < B200_STACK) stack[sp++] = c1, prefetch_ref(S, c1, true);
+  // cannot overflow: the BVH4 is only used when 3 * depth <= B200_STACK (api.cu: up to three pushes per level)
+  if (k3 < INF32) stack[sp++] = c3, prefetch_ref(S, c3, true);
+  if (k2 < INF32) stack[sp++] = c2, prefetch_ref(S, c2, true);
+  if (k1 < INF32) stack[sp++] = c1, prefetch_ref(S, c1, true);
   return k0 < INF32 ? c0 : B200_DONE;
 }
 

@@ -402,7 +402,10 @@ DEV void cp_async_wait_all() {
 // only when every lane has found one), small values stop lanes that have found their leaf from idling through the node
 // steps of the slowest lane.  Finished lanes refill from the staged batch as before.
 template <int MAXREG, bool SPEC, int WARPS, int STAGES, bool WIDE, bool UNI = false>
-__global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, Pools P, HitRef *hits, WaveParams wp) {
+__global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, Pools P, HitRef *hits, WaveParams wp, const uint32_t *order) {
+  // order (may be null): a permutation of the live paths; batch b then holds paths order[32 b .. 32 b + 31] instead of 32 consecutive
+  // ones (the ray-reordering experiment, B200RT_OPT_RAY_SORT): the staging becomes a gather, everything after it is unchanged
+  __shared__ uint32_t stage_idx[WARPS][STAGES][32];
   const PathBuf cur = pool_cur(c, P);
 #if B200_PATH_PAIRED
   __shared__ __align__(32) double2 stage_mem[WARPS][STAGES][224]; // warp x stage x {3 columns x 32 paths x 2 quads, then q6 of 32 paths}: 3.5 KB
@@ -421,6 +424,20 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
     // a batch is 1 KB contiguous per 32-byte column: lane l copies 16-byte chunks l and 32 + l of each (fully coalesced)
     if (batch < n_batches) {
       const uint32_t i0 = batch * 32;
+      if (order) { // gather: slot s of the batch is path order[i0 + s]
+        const uint32_t mine = i0 + lane < n ? __ldg(order + i0 + lane) : 0u;
+        stage_idx[wib][stg][lane] = mine;
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+          const uint32_t ch = 32 * k + lane, slot = ch >> 1;
+          const uint32_t pidx = __shfl_sync(FULL, mine, slot);
+          if (i0 + slot < n) {
+#pragma unroll
+            for (int c = 0; c < 3; c++) cp_async16_stream(&stage_mem[wib][stg][64 * c + ch], cur.base + ((size_t)c * cur.capacity + pidx) * 2 + (ch & 1u), stream_pol);
+          }
+        }
+        if (i0 + lane < n) cp_async16_stream(&stage_mem[wib][stg][192 + lane], quad_ptr(cur, 6, mine), stream_pol);
+      } else {
 #pragma unroll
       for (int c = 0; c < 3; c++)
 #pragma unroll
@@ -429,6 +446,7 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
           if (i0 + (ch >> 1) < n) cp_async16_stream(&stage_mem[wib][stg][64 * c + ch], cur.base + ((size_t)c * cur.capacity + i0) * 2 + ch, stream_pol);
         }
       if (i0 + lane < n) cp_async16_stream(&stage_mem[wib][stg][192 + lane], quad_ptr(cur, 6, i0 + lane), stream_pol); // q6 only: q7 (throughput) stays in HBM
+      }
     }
 #else
     const uint32_t i = batch * 32 + lane;
@@ -533,7 +551,7 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
           const float4 q4 = *reinterpret_cast<const float4 *>(sm + 128), q5 = *reinterpret_cast<const float4 *>(sm + 160);
           const float4 q6 = *reinterpret_cast<const float4 *>(sm + 192);
 #endif
-          idx = base + slot;
+          idx = order ? stage_idx[wib][stg][slot] : base + slot;
           const uint32_t pixel = __float_as_uint(q6.y);
           if (pixel == B200_DEAD) { // a camera sample that produced no ray: nothing to trace, nothing to shade
             store_hit(hits, idx, 0.0, -2, -1);
@@ -641,6 +659,46 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
         break;
       }
     }
+  }
+}
+
+// Ray-reordering experiment (B200RT_OPT_RAY_SORT): one key per live path from its ray, so that paths with similar rays end up
+// in the same 32-ray batch of the extend kernel.  mode bit 0: direction octant (3 bits); bit 1: 4 x 4 cells per face of the
+// direction cube (2 + 4 bits: major axis, then the two minor components); bit 2: origin cell on a 16^3 grid over the scene
+// bounds (12 bits, Morton order).  The most significant bits are the direction (rays of one direction class together, ordered
+// by where they start).  Slots beyond n_cur get the largest key.
+DEV uint32_t morton3_4(uint32_t x, uint32_t y, uint32_t z) { // 4 bits per axis
+  uint32_t m = 0;
+#pragma unroll
+  for (int b = 0; b < 4; b++) m |= ((x >> b & 1u) << (3 * b)) | ((y >> b & 1u) << (3 * b + 1)) | ((z >> b & 1u) << (3 * b + 2));
+  return m;
+}
+__global__ void __launch_bounds__(256) k_sort_keys(const WaveCtl *c, Pools P, WaveParams wp, int mode, uint32_t *keys, uint32_t *vals, uint32_t capacity) {
+  const PathBuf cur = pool_cur(c, P);
+  const uint32_t n = c->n_cur;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < capacity; i += gridDim.x * blockDim.x) {
+    uint32_t key = 0xffffffffu;
+    if (i < n) {
+      double2 q0, q1, q2, q3;
+      ld256(quad_ptr(cur, 0, i), q0, q1);
+      ld256(quad_ptr(cur, 2, i), q2, q3);
+      const double ox = q0.x, oy = q0.y, oz = q1.x, dx = q1.y, dy = q2.x, dz = q2.y;
+      key = 0;
+      if (mode & 4) {
+        auto cell = [](double o, double bound) { const double u = (o / bound + 1.0) * 8.0; return (uint32_t)(u < 0 ? 0 : (u > 15 ? 15 : (int)u)); };
+        key = morton3_4(cell(ox, wp.bound[0]), cell(oy, wp.bound[1]), cell(oz, wp.bound[2]));
+      }
+      if (mode & 2) {
+        const double ax = fabs(dx), ay = fabs(dy), az = fabs(dz);
+        const int major = ax >= ay && ax >= az ? 0 : (ay >= az ? 1 : 2);
+        const double m = major == 0 ? ax : (major == 1 ? ay : az), u = (major == 0 ? dy : dx) / m, v = (major == 2 ? dy : dz) / m;
+        auto q4 = [](double t) { const int k = (int)((t + 1.0) * 2.0); return (uint32_t)(k < 0 ? 0 : (k > 3 ? 3 : k)); };
+        key |= ((uint32_t)major << 4 | q4(u) << 2 | q4(v)) << 12;
+      }
+      if (mode & 1) key |= ((dx < 0 ? 1u : 0u) | (dy < 0 ? 2u : 0u) | (dz < 0 ? 4u : 0u)) << 18;
+    }
+    keys[i] = key;
+    vals[i] = i;
   }
 }
 

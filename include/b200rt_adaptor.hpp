@@ -468,40 +468,48 @@ inline b200rt_camera flatten_camera(const camera &cam) {
 }
 
 #ifndef B200RT_ADAPTOR_NO_RENDER
-// Drop-in for camera::render (src/camera.h:135-176): same arguments, same P3 output, same
-// cam.image_ contents; the sample loop runs on the GPU.  Throws on any backend error.
-inline void render(camera &cam, std::ofstream &out, const hittable &world, const std::shared_ptr<const hittable> light = nullptr,
-                   int device = 0, uint64_t seed = 0x5EEDull) {
+// Drop-in for camera::render (src/camera.h:135-176): same arguments, same P3 output, same cam.image_ contents; the sample
+// loop runs on the GPUs listed in `devices` (CUDA ordinals): one device = b200rt_render; several = the frame split by sample
+// range across them with one NCCL reduce (b200rt_group_*, include/b200rt.h).  Throws on any backend error.
+inline void render(camera &cam, std::ofstream &out, const hittable &world, const std::shared_ptr<const hittable> light,
+                   const std::vector<int> &devices, uint64_t seed = 0x5EEDull) {
   if (!out) {
     std::cerr << "Fail to open file.\n"; // src/camera.h:144-147
     return;
   }
+  if (devices.empty()) throw std::runtime_error("b200rt: no device given");
   flattener fl;
   fl.run(world, light.get(), cam.background_.get());
   b200rt_scene_desc sd = fl.out.desc();
   b200rt_camera cd = flatten_camera(cam);
-  b200rt_ctx *ctx = nullptr;
+  b200rt_group *grp = nullptr;
   auto check = [&](int rc) {
     if (rc != B200RT_OK) {
       std::string msg = b200rt_last_error();
-      if (ctx) b200rt_destroy(ctx);
+      if (grp) b200rt_group_destroy(grp);
       throw std::runtime_error("b200rt: " + msg);
     }
   };
-  check(b200rt_create(device, &ctx));
-  check(b200rt_upload_scene(ctx, &sd));
-  check(b200rt_set_camera(ctx, &cd));
+  check(b200rt_group_create(devices.data(), (int)devices.size(), &grp));
+  check(b200rt_group_upload_scene(grp, &sd));
+  check(b200rt_group_set_camera(grp, &cd));
   std::vector<double> sum((size_t)cd.image_width * cd.image_height * 3);
-  check(b200rt_render(ctx, seed, 0, cd.samples_per_pixel, sum.data(), nullptr));
-  // output stage on the device: the header and one write_color line per pixel (src/camera.h:149-151, 174; src/color.h:22-36)
+  check(b200rt_group_render(grp, seed, 0, cd.samples_per_pixel, sum.data(), nullptr));
+  // output stage on the first device: the header and one write_color line per pixel (src/camera.h:149-151, 174; src/color.h:22-36)
+  b200rt_ctx *ctx = nullptr;
+  check(b200rt_group_context(grp, 0, &ctx));
   std::vector<char> text(b200rt_ppm_bound(cd.image_width, cd.image_height));
   size_t text_len = 0;
   check(b200rt_format_ppm(ctx, sum.data(), cd.samples_per_pixel, text.data(), text.size(), &text_len));
   check(b200rt_finalize(ctx, sum.data(), cd.samples_per_pixel, sum.data(), nullptr));
-  b200rt_destroy(ctx);
+  b200rt_group_destroy(grp);
   out.write(text.data(), (std::streamsize)text_len);
   cam.image_.resize((size_t)cd.image_width * cd.image_height); // pixel_color / spp, as camera::render leaves it (src/camera.h:169-170)
   for (size_t i = 0; i < cam.image_.size(); i++) cam.image_[i] = color(sum[3 * i], sum[3 * i + 1], sum[3 * i + 2]);
+}
+inline void render(camera &cam, std::ofstream &out, const hittable &world, const std::shared_ptr<const hittable> light = nullptr,
+                   int device = 0, uint64_t seed = 0x5EEDull) {
+  render(cam, out, world, light, std::vector<int>{device}, seed);
 }
 #endif
 

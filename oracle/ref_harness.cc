@@ -82,6 +82,12 @@ B200DYN(b200rt_render)
 B200DYN(b200rt_finalize)
 B200DYN(b200rt_ppm_bound)
 B200DYN(b200rt_format_ppm)
+B200DYN(b200rt_group_create)
+B200DYN(b200rt_group_destroy)
+B200DYN(b200rt_group_upload_scene)
+B200DYN(b200rt_group_set_camera)
+B200DYN(b200rt_group_render)
+B200DYN(b200rt_group_context)
 #undef B200DYN
 void *handle = nullptr;
 bool bind(const char *path, std::string &err) {
@@ -106,6 +112,12 @@ bool bind(const char *path, std::string &err) {
   B200DYN(b200rt_finalize)
   B200DYN(b200rt_ppm_bound)
   B200DYN(b200rt_format_ppm)
+  B200DYN(b200rt_group_create)
+  B200DYN(b200rt_group_destroy)
+  B200DYN(b200rt_group_upload_scene)
+  B200DYN(b200rt_group_set_camera)
+  B200DYN(b200rt_group_render)
+  B200DYN(b200rt_group_context)
 #undef B200DYN
   return true;
 }
@@ -119,6 +131,12 @@ bool bind(const char *path, std::string &err) {
 #define b200rt_finalize (*b200dyn::b200rt_finalize)
 #define b200rt_ppm_bound (*b200dyn::b200rt_ppm_bound)
 #define b200rt_format_ppm (*b200dyn::b200rt_format_ppm)
+#define b200rt_group_create (*b200dyn::b200rt_group_create)
+#define b200rt_group_destroy (*b200dyn::b200rt_group_destroy)
+#define b200rt_group_upload_scene (*b200dyn::b200rt_group_upload_scene)
+#define b200rt_group_set_camera (*b200dyn::b200rt_group_set_camera)
+#define b200rt_group_render (*b200dyn::b200rt_group_render)
+#define b200rt_group_context (*b200dyn::b200rt_group_context)
 #include "b200rt_adaptor.hpp"
 
 // ------------------------------------------------------------------------------------------------
@@ -1025,6 +1043,7 @@ size_t ref_write_colors(const double *rgb, int W, int H, char *out, size_t cap) 
 
 // b200::render(cam, out, world, light) — the binding of INTEGRATION.md — in place of cam.render(out, world, light).
 // `product_lib` = path of libb200rt.so, loaded here on first use.  Returns wall seconds, < 0 on error (ref_last_error()).
+// device >= 0: that one device; device < 0: the first -device devices of the box (the frame split across them).
 double ref_render_b200(int h, unsigned long long seed, int spp, int device, const char *ppm_path, double *rgb_linear, const char *product_lib) {
   scene *s = get(h);
   if (!s) return -1.0;
@@ -1036,7 +1055,12 @@ double ref_render_b200(int h, unsigned long long seed, int spp, int device, cons
   double secs = -3.0;
   try {
     auto t0 = std::chrono::steady_clock::now();
-    b200::render(cam, out, *s->world, s->light, device, seed);
+    std::vector<int> devices;
+    if (device >= 0)
+      devices.push_back(device);
+    else
+      for (int k = 0; k < -device; k++) devices.push_back(k);
+    b200::render(cam, out, *s->world, s->light, devices, seed);
     secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (rgb_linear)
       for (size_t i = 0; i < cam.image_.size(); i++)

@@ -476,3 +476,22 @@ def test_gltf_textured_mesh_uv_and_render(ctx, build_oracle):
     ctx.upload_scene(s2)
     flat, _ = ctx.render(21, 0, 16)
     assert np.abs(flat - img).max() > 0.1
+
+
+@pytest.mark.parametrize("n_devices", [1, 2])
+def test_reference_side_binding_over_several_devices(n_devices, tmp_path):
+    """b200::render(cam, out, world, light, devices) of include/b200rt_adaptor.hpp on live reference objects: with two devices
+    the frame is split by sample range inside b200rt_group_render; file and cam.image_ equal the one-device result."""
+    import refharness
+
+    if not refharness.available():
+        pytest.skip("oracle/_ref/libref_harness.so not built")
+    if n_devices > _n_gpus():
+        pytest.skip(f"needs {n_devices} GPUs")
+    rs = refharness.RefScene("rtow", width=64, spp=6, depth=12)
+    _, one = rs.render_b200(seed=7, device=0)
+    path = str(tmp_path / "multi.ppm")
+    _, many = rs.render_b200(seed=7, device=-n_devices, ppm_path=path)
+    assert np.allclose(one, many, rtol=1e-12, atol=1e-12) and one.sum() > 0
+    assert open(path, "rb").read().startswith(f"P3\n{rs.camera.image_width} {rs.camera.image_height}\n255\n".encode())
+    rs.close()
