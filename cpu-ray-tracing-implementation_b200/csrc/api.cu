@@ -133,7 +133,7 @@ struct b200rt_ctx {
   } w[B200_MAX_PIPELINES];
   cudaStream_t cap_stream = nullptr; // stream captures are recorded on (never executes anything)
   int l2_persist = 1;  // B200RT_OPT_L2_PERSIST
-  int tri_f32 = 2;     // B200RT_OPT_TRI_F32: 0 = binary64 rows, 2 = binary32 rows (default), 1 = binary32 rows repeated in leaf order (measured: no gain)
+  int tri_f32 = 1;     // B200RT_OPT_TRI_F32
   size_t hot_bytes = 0; // prefix of the scene arena that the traversal reads per node / leaf
   size_t l2_window_max = 0, l2_persist_max = 0;
   int ray_sort = 0;    // B200RT_OPT_RAY_SORT
@@ -403,16 +403,21 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     c->carveout_pct = (int)value;
     return B200RT_OK;
   case B200RT_OPT_L2_PERSIST: c->l2_persist = value != 0; return B200RT_OK;
-  case B200RT_OPT_TRI_F32:
-    if (value != 0 && value != 1 && value != 2) return fail(B200RT_ERR_INVALID, "triangle rows: 0 (binary64), 1 (binary32, also in leaf order) or 2 (binary32)");
-    c->tri_f32 = (int)value; // takes effect at the next b200rt_upload_scene
-    return B200RT_OK; // takes effect at the next b200rt_upload_scene
+  case B200RT_OPT_TRI_F32: c->tri_f32 = value != 0; return B200RT_OK; // takes effect at the next b200rt_upload_scene // takes effect at the next b200rt_upload_scene
   case B200RT_OPT_RAY_SORT:
     if (!(value >= 0 && value <= 7)) return fail(B200RT_ERR_INVALID, "ray sort mode must be in [0, 7]");
+#if !B200_RAY_SORT_EXPERIMENT
+    if (value != 0) return fail(B200RT_ERR_UNSUPPORTED, "the ray-reordering experiment is not compiled into this build (-DB200_RAY_SORT_EXPERIMENT=1)");
+#endif
     c->ray_sort = (int)value;
     for (auto &w : c->w) w.capacity = 0; // the sort buffers are allocated with the wave pools
     return B200RT_OK;
-  case B200RT_OPT_OCTANT_SORT: c->octant_sort = value != 0; return B200RT_OK;
+  case B200RT_OPT_OCTANT_SORT:
+#if !B200_OCTANT_SORT_EXPERIMENT
+    if (value != 0) return fail(B200RT_ERR_UNSUPPORTED, "the octant-grouping experiment is not compiled into this build (-DB200_OCTANT_SORT_EXPERIMENT=1)");
+#endif
+    c->octant_sort = value != 0;
+    return B200RT_OK;
   case B200RT_OPT_EXTEND_LOOP:
     if (value != 0 && value != 1) return fail(B200RT_ERR_INVALID, "extend loop must be 0 (while-while) or 1 (warp-uniform)");
     c->extend_loop = (int)value;
@@ -519,7 +524,7 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
     auto pad = [](size_t n) { return ((n ? n : 16) + 255) & ~(size_t)255; };
     size_t total = 0;
     total += pad(wide.size() * sizeof(BvhNode4)) + pad(bvh.nodes.size() * sizeof(BvhNode)) + pad(ordered.size() * sizeof(Entry)) + pad(ordered.size());
-    total += 2 * pad(tri32.size() * 4) + pad(ordered.size() * 48) + pad((size_t)d->n_tris * B200RT_TRI_STRIDE * 8) + pad((size_t)d->n_spheres * B200RT_SPHERE_STRIDE * 8) + pad((size_t)d->n_quads * B200RT_QUAD_STRIDE * 8);
+    total += pad(tri32.size() * 4) + pad((size_t)d->n_tris * B200RT_TRI_STRIDE * 8) + pad((size_t)d->n_spheres * B200RT_SPHERE_STRIDE * 8) + pad((size_t)d->n_quads * B200RT_QUAD_STRIDE * 8);
     total += pad(fs.chain_ops.size() * sizeof(ChainOp)) + pad(fs.chains.size() * sizeof(Chain)) + pad(fs.vol_inst.size() * sizeof(VolInst)) + pad(fs.bentries.size() * sizeof(Entry));
     total += pad((size_t)d->n_spheres * 4) + pad((size_t)d->n_quads * 4) + pad((size_t)d->n_tris * 4) + pad(d->n_volumes * sizeof(b200rt_volume));
     total += pad(d->n_materials * sizeof(b200rt_material)) + pad(d->n_textures * sizeof(b200rt_texture));
@@ -533,14 +538,10 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
       UP(bvh.nodes.data(), bvh.nodes.size(), &S.bvh, "bvh");
     UP(ordered.data(), ordered.size(), &S.entries, "entries");
   }
-  std::vector<float> tri32e; // the binary32 rows in leaf (entry) order: a leaf test fetches entry and vertices in parallel
-  if (!tri32.empty() && !use_device_builder && c->tri_f32 == 1) {
-    tri32e.assign(ordered.size() * 12, 0.0f);
-    for (size_t k = 0; k < ordered.size(); k++)
-      if (entry_kind(ordered[k]) == E_TRI) std::memcpy(&tri32e[k * 12], &tri32[(size_t)ordered[k].row * 12], 48);
-    const float *pe = nullptr;
-    UP(tri32e.data(), tri32e.size(), &pe, "tri32e");
-    S.tri32e = reinterpret_cast<const float4 *>(pe);
+  if (!tri32.empty()) {
+    const float *p32 = nullptr;
+    UP(tri32.data(), tri32.size(), &p32, "tri32");
+    S.tri32 = reinterpret_cast<const float4 *>(p32);
   }
   UP(d->spheres, (size_t)d->n_spheres * B200RT_SPHERE_STRIDE, &S.spheres, "spheres");
   UP(d->quads, (size_t)d->n_quads * B200RT_QUAD_STRIDE, &S.quads, "quads");
@@ -553,11 +554,6 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
     cudaGetLastError();
   }
   // ---- warm: read per finished ray / per shaded hit
-  if (!tri32.empty()) { // row order: volume boundaries, the mirror traversal
-    const float *p32 = nullptr;
-    UP(tri32.data(), tri32.size(), &p32, "tri32");
-    S.tri32 = reinterpret_cast<const float4 *>(p32);
-  }
   if (!tri32.empty()) UP(d->tris, (size_t)d->n_tris * B200RT_TRI_STRIDE, &S.tris, "tris"); // normals for finish_hit
   UP(d->sphere_mat, d->n_spheres, &S.sphere_mat, "sphere_mat");
   UP(d->quad_mat, d->n_quads, &S.quad_mat, "quad_mat");
@@ -816,18 +812,18 @@ int ensure_wave(b200rt_ctx::WaveSet &w, uint32_t capacity, bool mirror, bool sor
 // Persistent extend launch.  The shared-memory carve-out is requested explicitly (smallest configuration that holds the
 // resident CTAs): what is left of the 256 KB is the L1 that caches BVH nodes and primitives.
 template <class K>
-void launch_extend(K kernel, b200rt_ctx *c, b200rt_ctx::WaveSet &w, int ctas_per_sm, int threads, int smem_per_cta, cudaStream_t s, const Pools &cur, const WaveParams &wp) {
+void launch_extend(K kernel, b200rt_ctx *c, b200rt_ctx::WaveSet &w, int ctas_per_sm, int threads, int smem_per_cta, cudaStream_t s, const PathBuf &cur, const WaveParams &wp) {
   const int want_kb = (ctas_per_sm * (smem_per_cta + 1024) + 1023) / 1024;
   cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, c->carveout_pct >= 0 ? c->carveout_pct : std::min(100, (want_kb * 100 + 227) / 228));
   kernel<<<c->sm_count * ctas_per_sm, threads, 0, s>>>(w.ctl, c->S, cur, w.hits, wp, (const uint32_t *)(c->ray_sort ? w.sort_vals[1] : nullptr));
 }
 
 template <bool MIRROR>
-int launch_shades(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, int grid, const Pools &pools, double *accum, const WaveParams &wp) {
+int launch_shades(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, int grid, const PathBuf &cur, const PathBuf &nxt, double *accum, const WaveParams &wp) {
   int n = 0;
 #define SHADE(K)                                                                                                       \
   if (K == B200_Q_MISS ? wp.fused_miss == 0 : (c->kinds_present >> K & 1u))                                                                \
-  n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(w.ctl, c->S, pools, w.hits, w.recs, w.queues.q[K], accum, wp)
+  n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(w.ctl, c->S, cur, nxt, w.hits, w.recs, w.queues.q[K], accum, wp)
   SHADE(B200_Q_MISS);
   SHADE(B200RT_MAT_DIFFUSE_LIGHT);
   SHADE(B200RT_MAT_LAMBERTIAN);
@@ -844,22 +840,30 @@ int launch_shades(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, int gri
 // pipeline's shade kernels are meant to run beside it).  ext_events (may be NULL) receives an event pair around extend.
 // `more` (may be 0): the conditional handle of the graph while loop this wave is being captured into; the last kernel then
 // also decides whether the loop goes round again.
-int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, const DevCamera &cam, const WaveParams &wp, int g_gen, int g_ext,
+int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned long long wave, const DevCamera &cam, const WaveParams &wp, int g_gen, int g_ext,
                 double *d_rgb_sum, int ext_ctas, std::vector<cudaEvent_t> *ext_events, cudaGraphConditionalHandle more = 0) {
   const bool mirror = c->traversal == B200RT_TRAVERSAL_MIRROR;
-  const Pools &cur = w.pools; // which pool holds this wave is decided on the device (WaveCtl::waves & 1)
+  const PathBuf &cur = w.pools.b[wave & 1], &nxt = w.pools.b[(wave & 1) ^ 1];
   const bool compact = cam.c.mode == B200RT_CAM_FISHEYE; // the only camera with samples that produce no ray
   int n_gen_launches = 2;
   if (compact) {
     // dropped samples leave room in the wave: further passes top it up (each sees the n_cur / next_sample the last one left)
     const int passes = 2; // 1: -2.7 % on Fox, 3: same as 2 (profiles/r01_x_fox_gen_passes.txt)
     for (int k = 0; k < passes; k++) {
+#if B200_GENERATE_POOLS
+      k_generate<true><<<g_gen, 256, 0, s>>>(w.ctl, w.pools, (int)(wave & 1), cam, wp);
+#else
       k_generate<true><<<g_gen, 256, 0, s>>>(w.ctl, cur, cam, wp);
+#endif
       k_ctl_generated<<<1, 1, 0, s>>>(w.ctl, 1);
     }
     n_gen_launches = 2 * passes;
   } else {
+#if B200_GENERATE_POOLS
+    k_generate<false><<<g_gen, 256, 0, s>>>(w.ctl, w.pools, (int)(wave & 1), cam, wp);
+#else
     k_generate<false><<<g_gen, 256, 0, s>>>(w.ctl, cur, cam, wp);
+#endif
     k_ctl_generated<<<1, 1, 0, s>>>(w.ctl, 0);
   }
   const bool tail = !mirror && c->tail_paths > 0;
@@ -904,7 +908,7 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, const Dev
     }
   if (ext_events) CU(cudaEventRecord(ext_events->back(), s));
   if (!mirror) k_classify<<<g_gen, 256, 0, s>>>(w.ctl, w.hits, w.queues);
-  const int n_shade = mirror ? launch_shades<true>(c, w, s, g_ext, cur, d_rgb_sum, wp) : launch_shades<false>(c, w, s, g_ext, cur, d_rgb_sum, wp);
+  const int n_shade = mirror ? launch_shades<true>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp) : launch_shades<false>(c, w, s, g_ext, cur, nxt, d_rgb_sum, wp);
   if (more)
     k_ctl_swap_cond<<<1, 1, 0, s>>>(w.ctl, more);
   else
@@ -952,7 +956,13 @@ int ensure_wave_graph(b200rt_ctx *c, b200rt_ctx::WaveSet &w, const std::string &
   cudaGraph_t body = np.conditional.phGraph_out[0];
   l2_window_on_stream(c, c->cap_stream);
   CU(cudaStreamBeginCaptureToGraph(c->cap_stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
-  const int n = launch_wave(c, w, c->cap_stream, cam, wp, g_gen, g_ext, d_rgb_sum, ext_ctas, nullptr, more);
+  // the body = an even and an odd wave (pools are by-value kernel parameters, so a wave's launches differ with its parity); the
+  // second one decides whether the loop goes round again.  A frame that ends on an even wave pays for one empty odd wave.
+  int n = launch_wave(c, w, c->cap_stream, 0, cam, wp, g_gen, g_ext, d_rgb_sum, ext_ctas, nullptr, 0);
+  if (n >= 0) {
+    const int n2 = launch_wave(c, w, c->cap_stream, 1, cam, wp, g_gen, g_ext, d_rgb_sum, ext_ctas, nullptr, more);
+    n = n2 < 0 ? n2 : n; // launches per WAVE
+  }
   cudaGraph_t captured = nullptr;
   const cudaError_t e_end = cudaStreamEndCapture(c->cap_stream, &captured);
   if (n < 0) {
@@ -1116,7 +1126,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   for (;;) {
     for (int p = 0; p < n_pipe; p++) {
       if (done[p]) continue;
-      const int n = launch_wave(c, c->w[p], ps[p], cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas,
+      const int n = launch_wave(c, c->w[p], ps[p], wave, cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas,
                                 stats && n_pipe == 1 ? &ext_events : nullptr);
       if (n < 0) return n;
       launches += (unsigned long long)n;

@@ -285,8 +285,7 @@ DEV_COLD bool volume_t(const DevScene *Sp, const Entry &e, const Ray &r, double 
 #define B200_SPHERE_FASTPATH 0
 #endif
 // ---------------------------------------------------------------- one leaf entry: accepted t in [lo, hi]
-// pos = the entry's position in DevScene::entries (the BVH leaf order), or -1 when it is not one of those
-DEV bool entry_t(const DevScene &S, const Entry &e, int pos, const Ray &rw, double lo, double hi, const Stream &st, int bounce, double &t) {
+DEV bool entry_t(const DevScene &S, const Entry &e, const Ray &rw, double lo, double hi, const Stream &st, int bounce, double &t) {
   const int kind = entry_kind(e);
 #if B200_SPHERE_FASTPATH
   if (e.kind_chain == (uint32_t)E_SPHERE) return sphere_row_t(S, e.row, false, rw, lo, hi, t); // hot path: untransformed static sphere
@@ -297,15 +296,7 @@ DEV bool entry_t(const DevScene &S, const Entry &e, int pos, const Ray &rw, doub
   case E_SPHERE:
   case E_SPHERE_MOVING: return sphere_row_t(S, e.row, kind == E_SPHERE_MOVING, r, lo, hi, t); // one inlined copy for both
   case E_QUAD: return quad_row_t(S, e.row, r, lo, hi, t, a, b);
-  case E_TRI: { // a NaN t is a "hit" in the reference; only the mirror traversal reproduces that
-    if (S.tri32e && pos >= 0) { // vertices stored by entry position: their address does not wait for the entry's own load
-      const float4 *q = S.tri32e + (size_t)pos * 3;
-      V p0, p1, p2;
-      tri32_unpack(__ldg(q), __ldg(q + 1), __ldg(q + 2), p0, p1, p2);
-      return tri_core_t(p0, p1, p2, r, lo, hi, t) && t == t;
-    }
-    return tri_row_t(S, e.row, r, lo, hi, t) && t == t;
-  }
+  case E_TRI: return tri_row_t(S, e.row, r, lo, hi, t) && t == t; // a NaN t is a "hit" in the reference; only the mirror traversal reproduces that
   case E_VOLUME: return volume_t(S.self, e, r, lo, hi, st, bounce, t);
   }
   return false;

@@ -80,7 +80,6 @@ struct DevScene {
   const int32_t *quad_mat;
   const double *tris;
   const float4 *tri32; // non-null: the nine vertex coordinates of every triangle as binary32 (exactly representable), three float4 per row
-  const float4 *tri32e; // non-null: the same rows once more in the order of `entries` (row of entry k at 3 k; zero for entries that are no triangles)
   const int32_t *tri_mat;
   const double *tri_uv; // optional: per triangle {u0 v0 u1 v1 u2 v2} (b200rt_scene_desc::tri_uv)
   const b200rt_volume *volumes;

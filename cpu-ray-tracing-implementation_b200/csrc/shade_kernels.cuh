@@ -18,17 +18,25 @@ DEV void prefetch_l2(const void *p) {
   asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 #endif
 }
+// Experiment (-DB200_OCTANT_SORT_EXPERIMENT=1, then B200RT_OPT_OCTANT_SORT): survivors of a CTA iteration written grouped by the
+// octant of their new direction.  Measured (profiles/r02_j_octant_grouping.jsonl): within +-1 % on every scene, and the extra
+// code costs the 64-register shade kernels spills (+5 % on the lambertian kernel, profiles/r02_t_*): compiled out.
+#ifndef B200_OCTANT_SORT_EXPERIMENT
+#define B200_OCTANT_SORT_EXPERIMENT 0
+#endif
 #ifndef B200_SHADE_MINB
 #define B200_SHADE_MINB 8
 #endif
 // One launch per queue.  KIND = b200rt_material_kind of every hit in the queue, or B200_Q_MISS.
 template <int KIND, bool MIRROR>
-__global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevScene S, Pools P, const HitRef *hits, const Rec *recs,
+__global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevScene S, PathBuf cur, PathBuf nxt, const HitRef *hits, const Rec *recs,
                                                 const uint32_t *queue, double *accum, WaveParams wp) {
-  const PathBuf cur = pool_cur(c, P), nxt = pool_nxt(c, P);
   // survivors are appended to the other pool with ONE global atomic per CTA iteration (same-address atomics are the
   // scarce resource of this kernel family: see k_classify); double-buffered by iteration parity
-  __shared__ uint32_t s_cnt[2][4], s_base[2], s_oct[2][8][4];
+  __shared__ uint32_t s_cnt[2][4], s_base[2];
+#if B200_OCTANT_SORT_EXPERIMENT
+  __shared__ uint32_t s_oct[2][8][4];
+#endif
   const uint32_t n = c->q_count[KIND];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int par = 0;
@@ -90,6 +98,7 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
     }
     const unsigned smask = __ballot_sync(0xffffffffu, survives);
     uint32_t pos;
+#if B200_OCTANT_SORT_EXPERIMENT
     if (wp.octant_sort) {
       // The survivors of this CTA iteration (<= 128 neighbouring paths) are written grouped by the OCTANT of their new direction,
       // so that the 32-ray batches the extend kernel hands to a warp walk the tree in a similar order.  No extra memory traffic:
@@ -116,7 +125,9 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
       }
       __syncthreads();
       pos = s_base[par] + (oct < 8 ? s_oct[par][oct][warp] : 0u) + before;
-    } else {
+    } else
+#endif
+    {
       if (lane == 0) s_cnt[par][warp] = (uint32_t)__popc(smask);
       __syncthreads();
       if (threadIdx.x == 0) {
@@ -140,8 +151,7 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
 // (keyed by pixel, sample, bounce), so the contribution of every path is unchanged.  The last CTA to finish empties the
 // wave (n_cur = 0): the kernels that follow in the stream find nothing to do.  WaveCtl::tail_done counts the finished CTAs
 // (zeroed by k_ctl_init / k_ctl_generated; no other kernel touches it).
-__global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, Pools P, double *accum, WaveParams wp, uint32_t limit) {
-  const PathBuf cur = pool_cur(c, P);
+__global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, PathBuf cur, double *accum, WaveParams wp, uint32_t limit) {
   const uint32_t n = c->n_cur;
   if (n == 0 || n > limit || c->next_sample != c->total_samples) return;
   unsigned long long my_rays = 0;

@@ -109,7 +109,7 @@ DEV void leaf_test(const DevScene &S, int32_t ref, const Ray &r, double lo, doub
     e.kind_chain = (uint32_t)raw.x, e.row = raw.y, e.prim = raw.z, e.order = (uint32_t)raw.w;
     double t;
     // like the reference, later leaves see the interval shrunk to the best t so far (closed: ties get through)
-    if (entry_t(S, e, (int)(first + k), r, lo, best.entry < 0 ? hi : best.t, st, bounce, t)) {
+    if (entry_t(S, e, r, lo, best.entry < 0 ? hi : best.t, st, bounce, t)) {
       if (best.entry < 0 || t < best.t || (t == best.t && e.order > best.order)) {
         best.t = t;
         best.entry = (int32_t)(first + k);

@@ -24,7 +24,7 @@ namespace b200 {
 #define B200_DEAD 0xFFFFFFFFu
 
 struct WaveCtl {
-  unsigned long long next_sample, total_samples, rays, nan_samples, waves, extend_rays_dummy;
+  unsigned long long next_sample, total_samples, rays, nan_samples, waves, wave_live; // wave_live: this wave had paths to trace (an empty trailing wave of the graph loop is not counted)
   uint32_t n_cur, n_next, capacity, fetch; // fetch: next unclaimed 32-ray batch of the persistent extend kernel
   uint32_t q_count[8];
   uint32_t n_gen, tail_done; // n_gen: live paths appended by k_generate<COMPACT> in this wave; tail_done: CTAs of k_tail that have finished
@@ -55,13 +55,13 @@ DEV size_t quad_index(uint32_t capacity, int q, uint32_t i) {
 #endif
 }
 DEV const double2 *quad_ptr(const PathBuf &b, int q, uint32_t i) { return b.base + quad_index(b.capacity, q, i); }
-// The two pools of a pipeline.  Which one holds the current wave is decided ON THE DEVICE from the wave counter, so that the
-// launches of a wave are identical from wave to wave (and can be the body of a CUDA-graph while loop, api.cu).
+// The two pools of a pipeline: wave k reads pool k & 1 and appends its survivors to the other one.  The kernels get the pools
+// of their wave as plain by-value parameters (constant bank: no registers).  Selecting the pool on the device from the wave
+// counter was tried for the CUDA-graph loop and cost the 64-register shade kernels 40-60 bytes of extra spills (+5 % on the
+// lambertian kernel, profiles/r02_t_*); the graph's loop body holds an even and an odd wave instead (api.cu).
 struct Pools {
   PathBuf b[2];
 };
-DEV PathBuf pool_cur(const WaveCtl *c, const Pools &P) { return P.b[(int)(c->waves & 1ull)]; }
-DEV PathBuf pool_nxt(const WaveCtl *c, const Pools &P) { return P.b[(int)(c->waves & 1ull) ^ 1]; }
 
 struct WaveParams {
   uint64_t seed;
@@ -165,6 +165,7 @@ __global__ void k_ctl_init(WaveCtl *c, unsigned long long total, uint32_t capaci
   c->rays = 0;
   c->nan_samples = 0;
   c->waves = 0;
+  c->wave_live = 0;
   c->n_cur = 0;
   c->n_next = 0;
   c->capacity = capacity;
@@ -181,6 +182,7 @@ __global__ void k_ctl_generated(WaveCtl *c, int compact) {
   const uint32_t n = wave_refill(c);
   c->n_cur += compact ? c->n_gen : n;
   c->next_sample += n;
+  c->wave_live = c->n_cur != 0 ? 1ull : c->wave_live;
   c->fetch = 0;
   c->n_gen = 0;
   c->tail_done = 0;
@@ -191,7 +193,8 @@ __global__ void k_ctl_swap(WaveCtl *c) {
   c->rays += r;
   c->n_cur = c->n_next;
   c->n_next = 0;
-  c->waves++;
+  c->waves += c->wave_live;
+  c->wave_live = 0;
 }
 
 // The same roll-over as the last node of the CUDA-graph while loop (api.cu): the loop runs another wave while paths are
@@ -203,7 +206,8 @@ __global__ void k_ctl_swap_cond(WaveCtl *c, cudaGraphConditionalHandle more) {
   c->rays += r;
   c->n_cur = c->n_next;
   c->n_next = 0;
-  c->waves++;
+  c->waves += c->wave_live;
+  c->wave_live = 0;
   cudaGraphSetConditional(more, (c->n_cur != 0 || c->next_sample < c->total_samples) ? 1u : 0u);
 }
 #endif
@@ -213,8 +217,15 @@ __global__ void k_ctl_swap_cond(WaveCtl *c, cudaGraphConditionalHandle more) {
 // exactly 0; they are counted and DROPPED here instead of riding through extend and classify as dead slots (56 % of the Fox
 // config's samples).  Live paths are appended behind n_cur with one atomic per CTA iteration; k_ctl_generated adds n_gen.
 template <bool COMPACT>
-__global__ void __launch_bounds__(256) k_generate(WaveCtl *c, Pools P, DevCamera cam, WaveParams wp) {
-  const PathBuf cur = pool_cur(c, P);
+#ifndef B200_GENERATE_POOLS
+#define B200_GENERATE_POOLS 1 // the generate kernels select their pool from a by-value pair with a run-time parity: +5.7 % on the Fox config (k_generate<COMPACT> is 45 % of that frame), +-0 elsewhere (profiles/r02_w_generate_pools.jsonl)
+#endif
+#if B200_GENERATE_POOLS
+__global__ void __launch_bounds__(256) k_generate(WaveCtl *c, Pools P, int parity, DevCamera cam, WaveParams wp) {
+  const PathBuf cur = P.b[parity];
+#else
+__global__ void __launch_bounds__(256) k_generate(WaveCtl *c, PathBuf cur, DevCamera cam, WaveParams wp) {
+#endif
   const uint32_t n_new = wave_refill(c), n_cur = c->n_cur;
   const unsigned long long g0 = c->next_sample;
   __shared__ uint32_t warp_live[8], cta_base;
@@ -291,8 +302,7 @@ DEV void classify(WaveCtl *c, const Queues &Q, uint32_t i, int which) {
 }
 
 template <bool MIRROR>
-__global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, Pools P, HitRef *hits, Rec *recs, Queues Q, WaveParams wp) {
-  const PathBuf cur = pool_cur(c, P);
+__global__ void __launch_bounds__(128) k_extend(WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, Rec *recs, Queues Q, WaveParams wp) {
   const uint32_t n = c->n_cur;
   // whole warps iterate together so that the ballots in classify() see a full mask
   for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x) {
@@ -393,6 +403,9 @@ DEV void cp_async_wait_all() {
 // soon as its 32 rays have been taken into registers.  Shared memory is carved out of the L1 that caches the BVH, so the
 // smaller footprint (14 KB instead of 28 KB per CTA) is not free to give away: see DESIGN.md.
 // WIDE: the tree is the BVH4 of scene_dev.cuh (S.bvh4) instead of the BVH2.
+#ifndef B200_RAY_SORT_EXPERIMENT
+#define B200_RAY_SORT_EXPERIMENT 0
+#endif
 #ifndef B200_EXT_DYNAMIC
 #define B200_EXT_DYNAMIC 4 // largest number of batches claimed per atomic; 0 = static striding (profiles/r01_v_*)
 #endif
@@ -402,11 +415,16 @@ DEV void cp_async_wait_all() {
 // only when every lane has found one), small values stop lanes that have found their leaf from idling through the node
 // steps of the slowest lane.  Finished lanes refill from the staged batch as before.
 template <int MAXREG, bool SPEC, int WARPS, int STAGES, bool WIDE, bool UNI = false>
-__global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, Pools P, HitRef *hits, WaveParams wp, const uint32_t *order) {
+__global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevScene S, PathBuf cur, HitRef *hits, WaveParams wp, const uint32_t *order) {
   // order (may be null): a permutation of the live paths; batch b then holds paths order[32 b .. 32 b + 31] instead of 32 consecutive
-  // ones (the ray-reordering experiment, B200RT_OPT_RAY_SORT): the staging becomes a gather, everything after it is unchanged
+  // ones (the ray-reordering experiment, B200RT_OPT_RAY_SORT, compiled in with -DB200_RAY_SORT_EXPERIMENT=1): the staging becomes a
+  // gather, everything after it is unchanged.  Measured (profiles/r02_n_ray_sort_potential.jsonl): a full radix sort of the rays
+  // by direction and origin buys at most 11 % of the extend time (Sponza stand-in) and costs 8-13 % on the small scenes.
+#if B200_RAY_SORT_EXPERIMENT
   __shared__ uint32_t stage_idx[WARPS][STAGES][32];
-  const PathBuf cur = pool_cur(c, P);
+#else
+  order = nullptr;
+#endif
 #if B200_PATH_PAIRED
   __shared__ __align__(32) double2 stage_mem[WARPS][STAGES][224]; // warp x stage x {3 columns x 32 paths x 2 quads, then q6 of 32 paths}: 3.5 KB
 #else
@@ -424,6 +442,7 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
     // a batch is 1 KB contiguous per 32-byte column: lane l copies 16-byte chunks l and 32 + l of each (fully coalesced)
     if (batch < n_batches) {
       const uint32_t i0 = batch * 32;
+#if B200_RAY_SORT_EXPERIMENT
       if (order) { // gather: slot s of the batch is path order[i0 + s]
         const uint32_t mine = i0 + lane < n ? __ldg(order + i0 + lane) : 0u;
         stage_idx[wib][stg][lane] = mine;
@@ -437,7 +456,9 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
           }
         }
         if (i0 + lane < n) cp_async16_stream(&stage_mem[wib][stg][192 + lane], quad_ptr(cur, 6, mine), stream_pol);
-      } else {
+      } else
+#endif
+      {
 #pragma unroll
       for (int c = 0; c < 3; c++)
 #pragma unroll
@@ -551,7 +572,11 @@ __global__ void B200_MAXNREG(MAXREG) k_extend_persistent(const WaveCtl *c, DevSc
           const float4 q4 = *reinterpret_cast<const float4 *>(sm + 128), q5 = *reinterpret_cast<const float4 *>(sm + 160);
           const float4 q6 = *reinterpret_cast<const float4 *>(sm + 192);
 #endif
+#if B200_RAY_SORT_EXPERIMENT
           idx = order ? stage_idx[wib][stg][slot] : base + slot;
+#else
+          idx = base + slot;
+#endif
           const uint32_t pixel = __float_as_uint(q6.y);
           if (pixel == B200_DEAD) { // a camera sample that produced no ray: nothing to trace, nothing to shade
             store_hit(hits, idx, 0.0, -2, -1);
@@ -673,8 +698,7 @@ DEV uint32_t morton3_4(uint32_t x, uint32_t y, uint32_t z) { // 4 bits per axis
   for (int b = 0; b < 4; b++) m |= ((x >> b & 1u) << (3 * b)) | ((y >> b & 1u) << (3 * b + 1)) | ((z >> b & 1u) << (3 * b + 2));
   return m;
 }
-__global__ void __launch_bounds__(256) k_sort_keys(const WaveCtl *c, Pools P, WaveParams wp, int mode, uint32_t *keys, uint32_t *vals, uint32_t capacity) {
-  const PathBuf cur = pool_cur(c, P);
+__global__ void __launch_bounds__(256) k_sort_keys(const WaveCtl *c, PathBuf cur, WaveParams wp, int mode, uint32_t *keys, uint32_t *vals, uint32_t capacity) {
   const uint32_t n = c->n_cur;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < capacity; i += gridDim.x * blockDim.x) {
     uint32_t key = 0xffffffffu;

@@ -248,9 +248,8 @@ typedef enum b200rt_option {
   B200RT_OPT_LEAF_LANES = 18,  /* tuning: see B200RT_OPT_EXTEND_LOOP (1..32, default 8; 32 = the while-while schedule) */
   B200RT_OPT_L2_PERSIST = 19,  /* 1 (default): the tree, the leaf entries and the primitive rows are uploaded into one address range that the render
                                   kernels declare as a persisting L2 access-policy window (the wave's path state streams past it) */
-  B200RT_OPT_TRI_F32 = 20,     /* 2 (default): triangle vertices are kept as 48-byte binary32 rows when every coordinate is exactly representable
-                                  (glTF positions are), and widened after the load: identical binary64 operands, 40 % fewer bytes per test;
-                                  0 = the 96-byte binary64 rows; 1 = binary32 rows stored a second time in leaf order (measured: no gain) */
+  B200RT_OPT_TRI_F32 = 20,     /* 1 (default): triangle vertices are kept as 48-byte binary32 rows when every coordinate is exactly representable
+                                  (glTF positions are), and widened after the load: identical binary64 operands, 40 % fewer bytes per test */
   B200RT_OPT_OCTANT_SORT = 21, /* tuning: 1 = the shade kernels write the surviving paths of a CTA iteration grouped by the octant of their new
                                   direction (more coherent 32-ray batches for the extend kernel; same paths, same samples) */
   B200RT_OPT_RAY_SORT = 22,    /* experiment: 0 (default) = off; else the live paths of every wave are radix-sorted by a key of their ray before the

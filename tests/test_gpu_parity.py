@@ -252,10 +252,10 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
         for opts in ({abi.OPT_SPECULATIVE_LEAF: 1}, {abi.OPT_REFILL_LANES: 12}, {abi.OPT_SPECULATIVE_LEAF: 1, abi.OPT_REFILL_LANES: 20}, {abi.OPT_FUSE_MISS: 0},
                      {abi.OPT_EXTEND_BLOCKS: 9}, {abi.OPT_EXTEND_STAGES: 1}, {abi.OPT_SMEM_CARVEOUT: 100}, {abi.OPT_WAVE_LOOP: 0},
                      {abi.OPT_EXTEND_LOOP: 1}, {abi.OPT_EXTEND_LOOP: 1, abi.OPT_LEAF_LANES: 1}, {abi.OPT_EXTEND_LOOP: 1, abi.OPT_LEAF_LANES: 32, abi.OPT_REFILL_LANES: 8},
-                     {abi.OPT_EXTEND_LOOP: 1, abi.OPT_BVH_WIDTH: 4}, {abi.OPT_OCTANT_SORT: 1}, {abi.OPT_L2_PERSIST: 0}):
+                     {abi.OPT_EXTEND_LOOP: 1, abi.OPT_BVH_WIDTH: 4}, {abi.OPT_L2_PERSIST: 0}, {abi.OPT_TRI_F32: 0}):
             for k, v in opts.items():
                 ctx.set_option(k, v)
-            if abi.OPT_BVH_WIDTH in opts:  # takes effect at upload
+            if abi.OPT_BVH_WIDTH in opts or abi.OPT_TRI_F32 in opts:  # take effect at upload
                 ctx.upload_scene(g.scene)
             img, st2 = ctx.render(77, 0, 6)
             ctx.set_option(abi.OPT_SPECULATIVE_LEAF, 0)
@@ -267,9 +267,9 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
             ctx.set_option(abi.OPT_WAVE_LOOP, 1)
             ctx.set_option(abi.OPT_EXTEND_LOOP, 0)
             ctx.set_option(abi.OPT_LEAF_LANES, 8)
-            ctx.set_option(abi.OPT_OCTANT_SORT, 0)
+            ctx.set_option(abi.OPT_TRI_F32, 1)
             ctx.set_option(abi.OPT_L2_PERSIST, 1)
-            if abi.OPT_BVH_WIDTH in opts:
+            if abi.OPT_BVH_WIDTH in opts or abi.OPT_TRI_F32 in opts:
                 ctx.set_option(abi.OPT_BVH_WIDTH, 0)
                 ctx.upload_scene(g.scene)
             assert st2["rays"] == st["rays"], opts

@@ -1,5 +1,6 @@
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_config_parity.py -m gpu -q -x -k "fox or sponza or gltf" > gpurun_out/r02p_pytest.log 2>&1; echo "rc=$?" >> gpurun_out/r02p_pytest.log
-for o in 1 2 0; do python tools/bench_scenes.py --scenes fox,sponza --reps 3 --opt 20=$o >> gpurun_out/r02p_sweep.jsonl 2>&1; done
-for l in 1 3 4; do python tools/bench_scenes.py --scenes sponza --reps 2 --opt 3=$l >> gpurun_out/r02p_sweep.jsonl 2>&1; done
-tail -3 gpurun_out/r02p_pytest.log
+timeout 900 python -m pytest tests -m gpu -q > gpurun_out/r02x_pytest.log 2>&1; echo "rc=$?" >> gpurun_out/r02x_pytest.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02x_smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/r02x_smoke.log
+python bench.py > gpurun_out/r02x_bench.json 2> gpurun_out/r02x_bench.err
+python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r02x_bench_ref.json 2> gpurun_out/r02x_bench_ref.err
+tail -3 gpurun_out/r02x_pytest.log; tail -2 gpurun_out/r02x_smoke.log
