@@ -98,6 +98,7 @@ struct b200rt_ctx {
   double scene_h2d_bytes = 0;
   int graph_depth = 0;
   int bg_mode = 0; // WaveParams::fused_miss for this scene
+  bool scene_optins = false; // the scene uses float images, bilinear lookups or triangle texture coordinates: the EXT kernels run
   uint32_t n_materials = 0;
   uint32_t kinds_present = 0; // bit k: some material of the scene has b200rt_material_kind k (queues of absent kinds stay empty)
   // camera
@@ -615,6 +616,9 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   c->kinds_present = 0;
   for (uint32_t i = 0; i < d->n_materials; i++) c->kinds_present |= 1u << d->materials[i].kind;
   c->bg_mode = d->background_tex < 0 ? 1 : 0;
+  c->scene_optins = d->tri_uv != nullptr;
+  for (uint32_t i = 0; i < d->n_textures; i++) c->scene_optins |= d->textures[i].kind == B200RT_TEX_PICTURE_LINEAR;
+  for (uint32_t i = 0; i < d->n_images; i++) c->scene_optins |= d->images[i].bytes_per_pixel >= 12;
   c->have_scene = true;
   return B200RT_OK;
 }
@@ -823,7 +827,7 @@ int launch_shades(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, int gri
   int n = 0;
 #define SHADE(K)                                                                                                       \
   if (K == B200_Q_MISS ? wp.fused_miss == 0 : (c->kinds_present >> K & 1u))                                                                \
-  n++, k_shade<K, MIRROR><<<grid, 128, 0, s>>>(w.ctl, c->S, cur, nxt, w.hits, w.recs, w.queues.q[K], accum, wp)
+  n++, (c->scene_optins ? k_shade<K, MIRROR, true> : k_shade<K, MIRROR, false>)<<<grid, 128, 0, s>>>(w.ctl, c->S, cur, nxt, w.hits, w.recs, w.queues.q[K], accum, wp)
   SHADE(B200_Q_MISS);
   SHADE(B200RT_MAT_DIFFUSE_LIGHT);
   SHADE(B200RT_MAT_LAMBERTIAN);
@@ -867,7 +871,7 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
     k_ctl_generated<<<1, 1, 0, s>>>(w.ctl, 0);
   }
   const bool tail = !mirror && c->tail_paths > 0;
-  if (tail) k_tail<<<(int)((c->tail_paths + 63) / 64), 64, 0, s>>>(w.ctl, c->S, cur, d_rgb_sum, wp, c->tail_paths);
+  if (tail) (c->scene_optins ? k_tail<true> : k_tail<false>)<<<(int)((c->tail_paths + 63) / 64), 64, 0, s>>>(w.ctl, c->S, cur, d_rgb_sum, wp, c->tail_paths);
   if (c->ray_sort && !mirror) { // experiment: a full radix sort per wave (its cost is not the point: the extend time after it is)
     k_sort_keys<<<g_gen, 256, 0, s>>>(w.ctl, cur, wp, c->ray_sort, w.sort_keys[0], w.sort_vals[0], w.capacity);
     CU(cub::DeviceRadixSort::SortPairs(w.sort_tmp, w.sort_tmp_bytes, w.sort_keys[0], w.sort_keys[1], w.sort_vals[0], w.sort_vals[1], (int)w.capacity, 0, 21, s));
@@ -1111,7 +1115,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
       std::string key;
       key_add(key, c->S), key_add(key, cam), key_add(key, wp[p]), key_add(key, cap[p]), key_add(key, d_rgb_sum), key_add(key, ext_ctas);
       key_add(key, c->tail_paths), key_add(key, c->extend_blocks), key_add(key, c->speculative), key_add(key, c->extend_stages), key_add(key, c->carveout_pct), key_add(key, c->extend_loop), key_add(key, c->l2_persist), key_add(key, c->ray_sort);
-      key_add(key, c->kinds_present), key_add(key, c->w[p].pools), key_add(key, c->w[p].hits);
+      key_add(key, c->kinds_present), key_add(key, c->scene_optins), key_add(key, c->w[p].pools), key_add(key, c->w[p].hits);
       if ((rc = ensure_wave_graph(c, c->w[p], key, cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas)) != B200RT_OK) return rc;
       CU(cudaGraphLaunch(c->w[p].graph_exec, ps[p]));
       if (stats) CU(cudaMemcpyAsync(c->w[p].h_ctl, c->w[p].ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, ps[p]));

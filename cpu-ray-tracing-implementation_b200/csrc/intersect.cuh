@@ -307,12 +307,12 @@ DEV bool entry_t(const DevScene &S, const Entry &e, const Ray &rw, double lo, do
 // the only texture::sample that looks at u, v: src/texture.h:12-119), which spares the shading kernels acos + atan2 per sphere hit.
 #define B200_UV_ALWAYS 1
 #define B200_UV_IF_USED 2
-DEV bool material_reads_uv(const DevScene &S, int mat) {
+template <bool EXT = true> DEV bool material_reads_uv(const DevScene &S, int mat) {
   const int k = S.textures[S.materials[mat].tex].kind;
-  return k == B200RT_TEX_PICTURE || k == B200RT_TEX_PICTURE_LINEAR;
+  return k == B200RT_TEX_PICTURE || (EXT && k == B200RT_TEX_PICTURE_LINEAR);
 }
 
-DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, Rec &rec, int uv_mode = B200_UV_ALWAYS) {
+template <bool EXT = true> DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, Rec &rec, int uv_mode = B200_UV_ALWAYS) {
   const int chain = entry_chain(e);
   const Ray r = chain_apply(S, chain, rw);
   rec.t = t;
@@ -326,7 +326,7 @@ DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, 
     const double *q = S.spheres + (size_t)e.row * B200RT_SPHERE_STRIDE;
     const V outward = (rec.p - v3(q[0], q[1], q[2])) / q[3]; // center_, also for moving spheres: src/sphere.h:69
     rec.mat = S.sphere_mat[e.row];
-    if (uv_mode == B200_UV_ALWAYS || material_reads_uv(S, rec.mat)) get_sphere_uv(outward, rec.u, rec.v);
+    if (uv_mode == B200_UV_ALWAYS || material_reads_uv<EXT>(S, rec.mat)) get_sphere_uv(outward, rec.u, rec.v);
     set_face_normal(rec, r, outward);
     break;
   }
@@ -335,7 +335,7 @@ DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, 
     const V p = rec.p - v3(q[0], q[1], q[2]);
     const V w = v3(q[12], q[13], q[14]);
     rec.mat = S.quad_mat[e.row];
-    if (uv_mode == B200_UV_ALWAYS || material_reads_uv(S, rec.mat)) {
+    if (uv_mode == B200_UV_ALWAYS || material_reads_uv<EXT>(S, rec.mat)) {
       rec.u = dot(w, cross(p, v3(q[6], q[7], q[8])));
       rec.v = dot(w, cross(v3(q[3], q[4], q[5]), p));
     }
@@ -346,7 +346,7 @@ DEV void finish_hit(const DevScene &S, const Entry &e, const Ray &rw, double t, 
     const double *q = S.tris + (size_t)e.row * B200RT_TRI_STRIDE;
     set_face_normal(rec, r, v3(q[9], q[10], q[11]));
     rec.mat = S.tri_mat[e.row];
-    if (S.tri_uv && (uv_mode == B200_UV_ALWAYS || material_reads_uv(S, rec.mat))) {
+    if (EXT && S.tri_uv && (uv_mode == B200_UV_ALWAYS || material_reads_uv<EXT>(S, rec.mat))) {
       // opt-in: vertex texture coordinates weighted with moller_trumbore's b0, b1 (src/triangle.h:8-15), recomputed for the hit
       const V p0 = v3(q[0], q[1], q[2]), p1 = v3(q[3], q[4], q[5]), p2 = v3(q[6], q[7], q[8]);
       const V e1 = p1 - p0, e2 = p2 - p0, sv = r.o - p0;

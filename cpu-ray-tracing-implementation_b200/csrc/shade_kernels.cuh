@@ -28,7 +28,7 @@ DEV void prefetch_l2(const void *p) {
 #define B200_SHADE_MINB 8
 #endif
 // One launch per queue.  KIND = b200rt_material_kind of every hit in the queue, or B200_Q_MISS.
-template <int KIND, bool MIRROR>
+template <int KIND, bool MIRROR, bool EXT>
 __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevScene S, PathBuf cur, PathBuf nxt, const HitRef *hits, const Rec *recs,
                                                 const uint32_t *queue, double *accum, WaveParams wp) {
   // survivors are appended to the other pool with ONE global atomic per CTA iteration (same-address atomics are the
@@ -73,17 +73,17 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
       sample = ph.sample;
       bounce = ph.bounce;
       if (KIND == B200_Q_MISS) {
-        accumulate(accum, pixel, T * miss_color(S, r));
+        accumulate(accum, pixel, T * miss_color<EXT>(S, r));
       } else {
         Rec rec;
         if (MIRROR) {
           rec = recs[i];
         } else {
           const HitRef h = hits[i];
-          finish_hit(S, S.entries[h.entry], r, h.t, rec, B200_UV_IF_USED);
+          finish_hit<EXT>(S, S.entries[h.entry], r, h.t, rec, B200_UV_IF_USED);
         }
         const Stream st{wp.seed, pixel, sample};
-        const Scatter sc = shade_hit<KIND>(S, rec, r, st, (int)bounce);
+        const Scatter sc = shade_hit<KIND, Stream, EXT>(S, rec, r, st, (int)bounce);
         if (sc.ends) {
           accumulate(accum, pixel, T * sc.value);
         } else {
@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(128, B200_SHADE_MINB) k_shade(WaveCtl *c, DevS
 // (keyed by pixel, sample, bounce), so the contribution of every path is unchanged.  The last CTA to finish empties the
 // wave (n_cur = 0): the kernels that follow in the stream find nothing to do.  WaveCtl::tail_done counts the finished CTAs
 // (zeroed by k_ctl_init / k_ctl_generated; no other kernel touches it).
+template <bool EXT>
 __global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, PathBuf cur, double *accum, WaveParams wp, uint32_t limit) {
   const uint32_t n = c->n_cur;
   if (n == 0 || n > limit || c->next_sample != c->total_samples) return;
@@ -166,20 +167,20 @@ __global__ void B200_MAXNREG(224) k_tail(WaveCtl *c, DevScene S, PathBuf cur, do
       const Best b = trace_closest(S, r, 0.001, B200_INF, st, bounce);
       my_rays++;
       if (b.entry < 0) {
-        accumulate(accum, ph.pixel, T * miss_color(S, r));
+        accumulate(accum, ph.pixel, T * miss_color<EXT>(S, r));
         break;
       }
       const Entry e = S.entries[b.entry];
       Rec rec;
-      finish_hit(S, e, r, b.t, rec, B200_UV_IF_USED);
+      finish_hit<EXT>(S, e, r, b.t, rec, B200_UV_IF_USED);
       Scatter sc;
       switch (S.materials[entry_material(S, e)].kind) {
-      case B200RT_MAT_DIFFUSE_LIGHT: sc = shade_hit<B200RT_MAT_DIFFUSE_LIGHT>(S, rec, r, st, bounce); break;
-      case B200RT_MAT_LAMBERTIAN: sc = shade_hit<B200RT_MAT_LAMBERTIAN>(S, rec, r, st, bounce); break;
-      case B200RT_MAT_METAL: sc = shade_hit<B200RT_MAT_METAL>(S, rec, r, st, bounce); break;
-      case B200RT_MAT_DIELECTRIC: sc = shade_hit<B200RT_MAT_DIELECTRIC>(S, rec, r, st, bounce); break;
-      case B200RT_MAT_GLOSS: sc = shade_hit<B200RT_MAT_GLOSS>(S, rec, r, st, bounce); break;
-      default: sc = shade_hit<B200RT_MAT_ISOTROPIC>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_DIFFUSE_LIGHT: sc = shade_hit<B200RT_MAT_DIFFUSE_LIGHT, Stream, EXT>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_LAMBERTIAN: sc = shade_hit<B200RT_MAT_LAMBERTIAN, Stream, EXT>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_METAL: sc = shade_hit<B200RT_MAT_METAL, Stream, EXT>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_DIELECTRIC: sc = shade_hit<B200RT_MAT_DIELECTRIC, Stream, EXT>(S, rec, r, st, bounce); break;
+      case B200RT_MAT_GLOSS: sc = shade_hit<B200RT_MAT_GLOSS, Stream, EXT>(S, rec, r, st, bounce); break;
+      default: sc = shade_hit<B200RT_MAT_ISOTROPIC, Stream, EXT>(S, rec, r, st, bounce); break;
       }
       if (sc.ends) {
         accumulate(accum, ph.pixel, T * sc.value);

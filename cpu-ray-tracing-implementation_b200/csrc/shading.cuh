@@ -87,7 +87,7 @@ DEV V light_random(const DevScene &S, V origin, double u1, double u2) {
 }
 
 // camera::miss: a unit sphere around the ray origin gives (u, v, p) for the background texture
-DEV V miss_color(const DevScene &S, const Ray &r) {
+template <bool EXT = true> DEV V miss_color(const DevScene &S, const Ray &r) {
   if (S.background_tex < 0) return v3(0, 0, 0);
   double t;
   if (!sphere_t(r.o, 1.0, r, 0.001, B200_INF, t)) return v3(0, 0, 0);
@@ -99,7 +99,7 @@ DEV V miss_color(const DevScene &S, const Ray &r) {
   const V outward = (p - r.o) / 1.0;
   double u, v;
   get_sphere_uv(outward, u, v);
-  return tex_sample(S, S.background_tex, u, v, p);
+  return tex_sample<EXT>(S, S.background_tex, u, v, p);
 }
 
 // Outcome of shading one hit.
@@ -125,7 +125,7 @@ struct FixedDraws {
 // One level of ray_color below the hit test (src/camera.h:202-240).  `b` = scatters so far on this path.
 // KIND >= 0: the caller knows the material kind at compile time (material-sorted queues), so only that branch is compiled in.
 // STREAM: where the draws come from (Stream = Philox by path address).  det: optional breakdown (constant nullptr on the hot path).
-template <int KIND = -1, class STREAM = Stream>
+template <int KIND = -1, class STREAM = Stream, bool EXT = true>
 DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const STREAM &st, int b, ScatterDetail *det = nullptr) {
   Scatter out;
   if (det) det->mode = 0, det->emitted = v3(0, 0, 0), det->attenuation = v3(0, 0, 0), det->pdf_value = 0, det->p_scattered = 0;
@@ -133,7 +133,7 @@ DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const STR
   if (KIND >= 0) m.kind = KIND;
   if (m.kind == B200RT_MAT_DIFFUSE_LIGHT) { // src/material.h:211-215; scatter() is the base's false (:43)
     out.ends = true;
-    out.value = rec.front_face ? tex_sample(S, m.tex, rec.u, rec.v, rec.p) : v3(0, 0, 0);
+    out.value = rec.front_face ? tex_sample<EXT>(S, m.tex, rec.u, rec.v, rec.p) : v3(0, 0, 0);
     out.dir = v3(0, 0, 0);
     if (det) det->emitted = out.value;
     return out;
@@ -144,7 +144,7 @@ DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const STR
   int pdf_kind = 0; // 1 cosine about the normal, 2 uniform sphere
   switch (m.kind) {
   case B200RT_MAT_LAMBERTIAN: // src/material.h:62-67
-    attenuation = tex_sample(S, m.tex, rec.u, rec.v, rec.p);
+    attenuation = tex_sample<EXT>(S, m.tex, rec.u, rec.v, rec.p);
     pdf_kind = 1;
     break;
   case B200RT_MAT_METAL: { // src/material.h:85-92: always scatters, fuzz draw taken even when fuzz == 0
@@ -153,12 +153,12 @@ DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const STR
     dir = dir + (double)m.p0 * unit_vector(random_in_unit_sphere(dm.u1, dm.u2));
     determined = true;
     out.dir = dir;
-    attenuation = tex_sample(S, m.tex, rec.u, rec.v, rec.p);
+    attenuation = tex_sample<EXT>(S, m.tex, rec.u, rec.v, rec.p);
     break;
   }
   case B200RT_MAT_DIELECTRIC: { // src/material.h:113-131, Schlick :135-139
     determined = true;
-    attenuation = tex_sample(S, m.tex, rec.u, rec.v, rec.p);
+    attenuation = tex_sample<EXT>(S, m.tex, rec.u, rec.v, rec.p);
     const double ri = rec.front_face ? (1.0 / m.p0) : m.p0;
     const V ud = unit_vector(r.d);
     const double cos_theta = fmin(dot(-ud, rec.normal), 1.0);
@@ -183,13 +183,13 @@ DEV Scatter shade_hit(const DevScene &S, const Rec &rec, const Ray &r, const STR
       determined = true;
       attenuation = v3(1.0, 1.0, 1.0);
     } else {
-      attenuation = tex_sample(S, m.tex, rec.u, rec.v, rec.p);
+      attenuation = tex_sample<EXT>(S, m.tex, rec.u, rec.v, rec.p);
       pdf_kind = 1;
     }
     break;
   }
   default: // B200RT_MAT_ISOTROPIC, src/material.h:193-200
-    attenuation = tex_sample(S, m.tex, rec.u, rec.v, rec.p);
+    attenuation = tex_sample<EXT>(S, m.tex, rec.u, rec.v, rec.p);
     pdf_kind = 2;
     break;
   }

@@ -84,9 +84,13 @@ DEV_COLD double worley_noise(V p, bool voronoi) { // src/noise.h:147-167, :179-2
 
 // One texel as a colour: 8-bit images as the reference reads them (byte / 256, src/texture.h:72-73), float images (12 or 16
 // bytes per pixel, the opt-in un-quantised ingest) as they are: no clamp, so an HDR environment keeps its values above 1.
-DEV V image_texel(const DevScene &S, const b200rt_image &im, int i, int j) {
+// EXT (here and in tex_sample / finish_hit / shade_hit): the scene uses one of the opt-in extensions (float images, bilinear
+// lookups, triangle texture coordinates).  The wavefront kernels are instantiated for both values and a scene without opt-ins
+// runs the EXT = false ones, whose code is the reference path only: with the extensions compiled into the 64-register shade
+// kernels, ptxas moved spills into the hot path (lambertian kernel +6.5 %, C2 -2 %; profiles/r02_ac_optins.jsonl).
+template <bool EXT = true> DEV V image_texel(const DevScene &S, const b200rt_image &im, int i, int j) {
   const uint8_t *px = S.image_bytes + im.offset + ((size_t)j * im.width + i) * im.bytes_per_pixel;
-  if (im.bytes_per_pixel >= 12) {
+  if (EXT && im.bytes_per_pixel >= 12) {
     const float *f = reinterpret_cast<const float *>(px);
     return v3((double)f[0], (double)f[1], (double)f[2]);
   }
@@ -94,7 +98,7 @@ DEV V image_texel(const DevScene &S, const b200rt_image &im, int i, int j) {
   return v3(px[0] * cs, px[1] * cs, px[2] * cs);
 }
 
-DEV V tex_sample(const DevScene &S, int tex, double u, double v, V p) {
+template <bool EXT = true> DEV V tex_sample(const DevScene &S, int tex, double u, double v, V p) {
   const b200rt_texture &t = S.textures[tex];
   switch (t.kind) {
   case B200RT_TEX_SOLID: return v3(t.c0[0], t.c0[1], t.c0[2]);
@@ -111,10 +115,11 @@ DEV V tex_sample(const DevScene &S, int tex, double u, double v, V p) {
     int j = (int)(im.height * (1 - v));
     i = i < 0 ? 0 : (i < im.width ? i : im.width - 1);
     j = j < 0 ? 0 : (j < im.height ? j : im.height - 1);
-    return image_texel(S, im, i, j);
+    return image_texel<EXT>(S, im, i, j);
   }
   case B200RT_TEX_PICTURE_LINEAR: { // opt-in: bilinear between texel centres, edges clamped
     const b200rt_image im = S.images[t.aux];
+    if (!EXT) return v3(0, 0, 0); // not reachable: scenes with this texture kind run the EXT kernels
     if (!im.has_data) return v3(255 / 256.0, 0.0, 255 / 256.0);
     const double x = im.width * u - 0.5, y = im.height * (1 - v) - 0.5;
     const double fx0 = floor(x), fy0 = floor(y);
@@ -122,7 +127,7 @@ DEV V tex_sample(const DevScene &S, int tex, double u, double v, V p) {
     const int W = im.width, H = im.height;
     auto cl = [](double f, int n) { return f < 0 ? 0 : (f > n - 1 ? n - 1 : (int)f); };
     const int i0 = cl(fx0, W), i1 = cl(fx0 + 1, W), j0 = cl(fy0, H), j1 = cl(fy0 + 1, H);
-    const V c00 = image_texel(S, im, i0, j0), c10 = image_texel(S, im, i1, j0), c01 = image_texel(S, im, i0, j1), c11 = image_texel(S, im, i1, j1);
+    const V c00 = image_texel<EXT>(S, im, i0, j0), c10 = image_texel<EXT>(S, im, i1, j0), c01 = image_texel<EXT>(S, im, i0, j1), c11 = image_texel<EXT>(S, im, i1, j1);
     const V top = (1 - ax) * c00 + ax * c10, bot = (1 - ax) * c01 + ax * c11;
     return (1 - ay) * top + ay * bot;
   }

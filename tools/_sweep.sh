@@ -1,6 +1,7 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q > gpurun_out/r02x_pytest.log 2>&1; echo "rc=$?" >> gpurun_out/r02x_pytest.log
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02x_smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/r02x_smoke.log
-python bench.py > gpurun_out/r02x_bench.json 2> gpurun_out/r02x_bench.err
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r02x_bench_ref.json 2> gpurun_out/r02x_bench_ref.err
-tail -3 gpurun_out/r02x_pytest.log; tail -2 gpurun_out/r02x_smoke.log
+timeout 900 python -m pytest tests -m gpu -q > gpurun_out/r02ad_pytest.log 2>&1; echo "rc=$?" >> gpurun_out/r02ad_pytest.log
+L=$PWD/cpu-ray-tracing-implementation_b200
+for rep in 1 2; do for v in "" _r01; do
+  B200RT_LIB=$L/libb200rt$v.so python tools/bench_scenes.py --scenes rtow,cornell,rtnw,fox,sponza --reps 3 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"build$v\"]/" >> gpurun_out/r02ad_vs_r01.jsonl
+done; done
+tail -3 gpurun_out/r02ad_pytest.log
