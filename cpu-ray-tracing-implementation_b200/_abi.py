@@ -167,6 +167,7 @@ EXPORTS = [
     "b200rt_abi_sizeof",
     "b200rt_image_bound",
     "b200rt_format_image",
+    "b200rt_format_ppm_noalloc",
     "b200rt_group_create",
     "b200rt_group_destroy",
     "b200rt_group_size",
@@ -179,6 +180,7 @@ EXPORTS = [
 ]
 GROUP_OPT_REDUCE, GROUP_REDUCE_NCCL, GROUP_REDUCE_PEER = 1000, 0, 1
 IMAGE_PPM_TEXT, IMAGE_PPM_BINARY, IMAGE_EXR = 0, 1, 2
+NOALLOC_MAX_PIXELS = 1 << 20  # B200RT_NOALLOC_MAX_PIXELS: b200rt_format_ppm_noalloc's static scratch
 
 
 class _Missing:
@@ -234,6 +236,7 @@ def _bind(lib):
     lib.b200rt_image_bound.argtypes = [i32, i32, i32]
     lib.b200rt_image_bound.restype = C.c_size_t
     lib.b200rt_format_image.argtypes = [vp, vp, i32, i32, vp, sz, C.POINTER(sz)]
+    lib.b200rt_format_ppm_noalloc.argtypes = [vp, vp, i32, vp, sz, C.POINTER(sz)]  # device pointers in and out
     lib.b200rt_group_create.argtypes = [C.POINTER(i32), i32, C.POINTER(vp)]
     lib.b200rt_group_destroy.argtypes = [vp]
     lib.b200rt_group_size.argtypes = [vp]

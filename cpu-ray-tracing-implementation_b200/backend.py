@@ -151,6 +151,12 @@ class Context:
         self._check(self._lib.b200rt_format_ppm(self._h, rgb_sum.ctypes.data, total_spp, buf.ctypes.data, cap, C.byref(n)))
         return buf[: n.value].tobytes()
 
+    def format_ppm_noalloc(self, d_rgb_sum, total_spp, d_out, capacity):
+        """b200rt_format_ppm_noalloc: DEVICE addresses in (W*H*3 doubles) and out (`capacity` bytes); -> the file's length.  The call
+        allocates nothing: its scratch is a static device array for images of at most abi.NOALLOC_MAX_PIXELS pixels."""
+        n = C.c_size_t(0)
+        self._check(self._lib.b200rt_format_ppm_noalloc(self._h, int(d_rgb_sum), total_spp, int(d_out), int(capacity), C.byref(n)))
+        return n.value
 
     def format_image(self, rgb_sum, total_spp, fmt, capacity=None):
         """The frame as a complete file image: abi.IMAGE_PPM_TEXT (the reference's P3), IMAGE_PPM_BINARY (P6) or IMAGE_EXR (linear float)."""

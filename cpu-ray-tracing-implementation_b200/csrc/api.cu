@@ -1377,3 +1377,4 @@ int b200rt_format_image(b200rt_ctx *c, const double *rgb_sum, int total_spp, int
 } // extern "C"
 
 #include "group.cuh"
+#include "noalloc.cuh"

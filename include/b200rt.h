@@ -339,6 +339,21 @@ typedef enum b200rt_image_format { B200RT_IMAGE_PPM_TEXT = 0, B200RT_IMAGE_PPM_B
 size_t b200rt_image_bound(int format, int image_width, int image_height);
 int b200rt_format_image(b200rt_ctx *ctx, const double *rgb_sum, int total_spp, int format, char *out, size_t capacity, size_t *out_len);
 
+/* No counterpart in the reference: added for callers that must not reach cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The same P3 file image as b200rt_format_ppm, produced by the
+ * same kernels, but this entry point allocates nothing: no cudaMalloc / cudaFree / allocating library routine on any path.
+ *   d_rgb_sum : DEVICE pointer, W*H*3 doubles (e.g. what b200rt_render_device accumulated); W, H = the context's camera
+ *   d_out     : DEVICE pointer, `capacity` bytes; receives the complete file image, header included
+ *   *out_len  : host; the file's length (also on B200RT_ERR_INVALID for a too small capacity: the size needed)
+ * The scratch of the two-pass formatter (three integers per pixel, per-CTA byte counts, the total: 12 bytes per pixel + 8.25 KiB) lives in
+ * a file-scope __device__ array sized for B200RT_NOALLOC_MAX_PIXELS pixels (12 MiB + 8.25 KiB, held by every GPU that loads the library
+ * until the process exits).  An image with more pixels fails with B200RT_ERR_UNSUPPORTED.  Every call on a device shares that array, and
+ * it keeps the previous call's contents: each call overwrites every word it later reads (nothing has to start at zero), but two calls
+ * that overlap on the same GPU (two contexts, two threads) race on it: serialise them.  Work is issued on the context's stream;
+ * the call returns after that stream has drained. */
+#define B200RT_NOALLOC_MAX_PIXELS (1u << 20)
+int b200rt_format_ppm_noalloc(b200rt_ctx *ctx, const double *d_rgb_sum, int total_spp, char *d_out, size_t capacity, size_t *out_len);
+
 /* Replaces: texture::sample(u, v, p) (src/texture.h:9) of texture row `tex` on a batch.
  * uvp5 = n x {u, v, p[3]}, rgb = n x 3.  Host buffers. */
 int b200rt_texture_sample(b200rt_ctx *ctx, int tex, const double *uvp5, size_t n, double *rgb);
