@@ -100,6 +100,23 @@ def test_textures_vs_reference_golden(ctx, name):
             assert same(rgb, ref).all(), f"{name}: texture {t}"
 
 
+def outlier_bounds(name, a, b, fin, close, spp):
+    """The pixels that do NOT agree to 1e-9 are those where one sample took another branch on a last-place libm difference (a
+    scatter decision, a volume free-flight distance).  Such a pixel differs by at most one or two whole samples, i.e. by no more
+    than 2 x (the brightest single sample of either image) / spp; the brightest sample is at most spp x the brightest pixel mean.
+    Anything larger (a dropped subtree, a wrong tie-break that moves many samples of a pixel) fails here."""
+    off = fin & ~close
+    if not off.any():
+        return
+    brightest_sample = spp * max(np.abs(a[fin]).max(), np.abs(b[fin]).max())
+    worst = np.abs(a - b)[off].max()
+    print(f"[{name}] {int(off.sum())} of {int(fin.sum())} values differ beyond 1e-9; largest difference {worst:.3g} (brightest sample <= {brightest_sample:.3g})")
+    assert worst <= 2.0 * brightest_sample / spp, f"{name}: an outlier differs by {worst}, more than two whole samples"
+    # and they are isolated events, not a region: no pixel row holds more than a few of them
+    rows = off.reshape(off.shape[0], -1).sum(axis=1)
+    assert rows.max() <= max(6, 0.05 * off[0].size), f"{name}: {rows.max()} differing values in one image row"
+
+
 def render_pair(ctx, oracle, g, seed, spp, mode=abi.TRAVERSAL_FAST, kill_zero=0):
     ctx.set_option(abi.OPT_TRAVERSAL, mode)
     ctx.set_option(abi.OPT_KILL_ZERO_WEIGHT, kill_zero)
@@ -119,10 +136,12 @@ def test_render_matches_oracle_sample_for_sample(ctx, name, build_oracle):
     spp = 8
     img, st, ref = render_pair(ctx, build_oracle, g, 4711, spp)
     a, b = img / spp, ref["sum"] / spp
-    fin = np.isfinite(a) & np.isfinite(b)
+    assert np.array_equal(np.isfinite(a), np.isfinite(b)), f"{name}: non-finite pixels differ from the oracle's"
+    fin = np.isfinite(b)
     assert fin.mean() > 0.995
     close = np.abs(a - b) <= 1e-9 * np.maximum(np.abs(b), 1e-3)
     assert close[fin].mean() > 0.995, f"{name}: only {close[fin].mean():.4f} of pixels agree to 1e-9"
+    outlier_bounds(name, a, b, fin, close, spp)
     rmse = np.sqrt(((a - b)[fin] ** 2).mean())
     assert rmse < 1e-3 * max(1.0, np.abs(b[fin]).max()), f"{name}: rmse {rmse}"
     assert abs(a[fin].mean() - b[fin].mean()) <= 0.005 * abs(b[fin].mean()) + 1e-12
@@ -136,9 +155,11 @@ def test_render_mirror_mode_matches_oracle(ctx, name, build_oracle):
     spp = 4
     img, st, ref = render_pair(ctx, build_oracle, g, 99, spp, mode=abi.TRAVERSAL_MIRROR)
     a, b = img / spp, ref["sum"] / spp
-    fin = np.isfinite(a) & np.isfinite(b)
+    assert np.array_equal(np.isfinite(a), np.isfinite(b)), f"{name}: non-finite pixels differ from the oracle's"
+    fin = np.isfinite(b)
     close = np.abs(a - b) <= 1e-9 * np.maximum(np.abs(b), 1e-3)
     assert close[fin].mean() > 0.995
+    outlier_bounds(name, a, b, fin, close, spp)
 
 
 @pytest.mark.parametrize("name", CONFIG_SCENES)
