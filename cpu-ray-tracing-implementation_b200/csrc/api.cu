@@ -887,7 +887,11 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
   if (mirror)
     k_extend<true><<<g_ext, 128, 0, s>>>(w.ctl, c->S, cur, w.hits, w.recs, w.queues, wp);
   else
-    switch (c->S.bvh4 ? 0 : c->extend_blocks * 2 + (c->speculative ? 1 : 0)) { // the tuning variants below walk the BVH2 only
+#ifndef B200_BVH4_OCCUPANCY_EXPERIMENT
+#define B200_BVH4_OCCUPANCY_EXPERIMENT 0 // 1: B200RT_OPT_EXTEND_BLOCKS 5 / 6 also select 96- / 80-register BVH4 kernels (measured: slower)
+#endif
+    switch (c->S.bvh4 ? (B200_BVH4_OCCUPANCY_EXPERIMENT && (c->extend_blocks == 5 || c->extend_blocks == 6) ? 100 + c->extend_blocks : 0)
+                      : c->extend_blocks * 2 + (c->speculative ? 1 : 0)) { // the other tuning variants walk the BVH2 only
     // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
 #define EXT(MAXREG, SPEC, WARPS, STAGES)                                                                               \
   launch_extend(k_extend_persistent<MAXREG, SPEC, WARPS, STAGES, false>, c, w, 65536 / (MAXREG * WARPS * 32), WARPS * 32, WARPS * STAGES * 3584, s, cur, wp)
@@ -897,6 +901,11 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
     case 34: EXT(120, false, 1, 1); break; // 17 warps (option value 17: 1-warp CTAs)
     case 9: EXT(128, true, 4, 2); break;
 #undef EXT
+#if B200_BVH4_OCCUPANCY_EXPERIMENT
+    // BVH4 at higher occupancy (latency-bound scenes: the Sponza stand-in waits on L2 with four warps per scheduler)
+    case 105: launch_extend(k_extend_persistent<96, false, 4, 2, true>, c, w, 5, 128, 4 * 2 * 3584, s, cur, wp); break; // 20 warps per SM
+    case 106: launch_extend(k_extend_persistent<80, false, 4, 2, true>, c, w, 6, 128, 4 * 2 * 3584, s, cur, wp); break; // 24 warps per SM
+#endif
     default: // 128 registers, 4-warp CTAs
       if (c->extend_loop == 1 && c->S.bvh4)
         launch_extend(k_extend_persistent<128, false, 4, 2, true, true>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);

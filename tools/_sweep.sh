@@ -1,7 +1,6 @@
-# scratch: same-box A/B of library builds (tools/bench_scenes.py picks the build up from B200RT_LIB)
+# scratch: BVH4 extend kernel at 20 / 24 warps per SM (B200RT_OPT_EXTEND_BLOCKS = 5 / 6) against the 16-warp default
 mkdir -p gpurun_out
-L=$PWD/cpu-ray-tracing-implementation_b200
-for rep in 1 2; do for v in "" _r01 _minb6 _minb7 _minb10 _minb12; do
-  B200RT_LIB=$L/libb200rt$v.so python tools/bench_scenes.py --scenes rtow,cornell,rtnw,fox,sponza --reps 3 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"build$v\"]/" >> gpurun_out/r02aj_builds_same_box.jsonl
+for rep in 1 2; do for o in "" "--opt 6=5" "--opt 6=6"; do
+  python tools/bench_scenes.py --scenes rtnw,sponza --reps 3 $o 2>&1 >> gpurun_out/r02an_bvh4_occupancy.jsonl
 done; done
-tail -n 3 gpurun_out/r02aj_builds_same_box.jsonl
+grep -o '"scene": "[a-z]*", "opts": [^]]*]\|"mrays_per_s": [0-9.]*' gpurun_out/r02an_bvh4_occupancy.jsonl | paste - -
