@@ -17,7 +17,7 @@ TEX_SOLID, TEX_CHECKER, TEX_PICTURE, TEX_PERLIN, TEX_VALUE, TEX_WORLEY, TEX_VORO
 LIGHT_NONE, LIGHT_QUAD, LIGHT_SPHERE, LIGHT_DEFAULT = 0, 1, 2, 3
 CAM_PERSPECTIVE, CAM_ORTHOGRAPHIC, CAM_FISHEYE, CAM_LENS = 0, 1, 2, 3
 OPT_TRAVERSAL, OPT_WAVE_PATHS, OPT_KILL_ZERO_WEIGHT, OPT_BVH_LEAF_SIZE, OPT_RESERVED_4, OPT_REFILL_LANES, OPT_EXTEND_BLOCKS, OPT_SPECULATIVE_LEAF, OPT_FUSE_MISS, OPT_EXTEND_STAGES, OPT_SMEM_CARVEOUT, OPT_BVH_BUILDER, OPT_BVH_WIDTH, OPT_PIPELINES, OPT_PIPE_EXTEND_CTAS, OPT_TAIL_PATHS, OPT_WAVE_LOOP, OPT_EXTEND_LOOP, OPT_LEAF_LANES, OPT_L2_PERSIST, OPT_TRI_F32, OPT_OCTANT_SORT, OPT_RAY_SORT = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22
-BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1
+BVH_HOST_SAH, BVH_DEVICE_LBVH, BVH_DEVICE_PLOC = 0, 1, 2
 TRAVERSAL_FAST, TRAVERSAL_MIRROR = 0, 1
 
 SPHERE_STRIDE, QUAD_STRIDE, TRI_STRIDE = 12, 20, 12

@@ -9,6 +9,7 @@
 
 #include "bvh_build.h"
 #include "bvh_gpu.cuh"
+#include "bvh_ploc.cuh"
 #include "output.cuh"
 #include "shade_kernels.cuh"
 
@@ -245,6 +246,91 @@ int build_bvh_device(b200rt_ctx *c, const FlatScene &fs, DevScene &S, b200rt_bvh
   return B200RT_OK;
 }
 
+// Device PLOC (bvh_ploc.cuh) + host finishing pass (bvh_build.h:finish_tree): the BVH2 topology is clustered on the device, comes back
+// (64 bytes per node), gets its leaf pairs, depth-first layout and, in b200rt_upload_scene, the BVH4 collapse on the host.  `out.perm`
+// indexes the flattener's entry order like the host builder's.  Returns B200RT_ERR_UNSUPPORTED if the clustering does not converge in
+// a sane number of rounds (the caller then falls back to the host builder).
+int build_bvh_ploc(b200rt_ctx *c, const FlatScene &fs, int max_leaf, BuiltBvh &out) {
+  const uint32_t n = (uint32_t)fs.boxes.size();
+  if (n >= (1u << 28)) return fail(B200RT_ERR_UNSUPPORTED, "device BVH build: %u primitives exceed the leaf reference range", n);
+  DevMem tmp;
+  cudaStream_t s = c->stream;
+  Box *d_boxes = nullptr;
+  uint32_t *codes[2] = {nullptr, nullptr}, *ids[2] = {nullptr, nullptr};
+  PlocCluster *cl[2] = {nullptr, nullptr};
+  int *nn = nullptr;
+  unsigned long long *flags = nullptr, *scan = nullptr;
+  unsigned int *totals = nullptr;
+  LbvhStats *st = nullptr;
+  BvhNode *nodes = nullptr;
+  const size_t ni = n > 1 ? n - 1 : 0;
+  CU(tmp.alloc((void **)&d_boxes, n * sizeof(Box)));
+  for (int k = 0; k < 2; k++) {
+    CU(tmp.alloc((void **)&codes[k], n * 4));
+    CU(tmp.alloc((void **)&ids[k], n * 4));
+    CU(tmp.alloc((void **)&cl[k], n * sizeof(PlocCluster)));
+  }
+  CU(tmp.alloc((void **)&nn, n * 4));
+  CU(tmp.alloc((void **)&flags, n * 8));
+  CU(tmp.alloc((void **)&scan, n * 8));
+  CU(tmp.alloc((void **)&totals, 8));
+  CU(tmp.alloc((void **)&st, sizeof(LbvhStats)));
+  CU(tmp.alloc((void **)&nodes, ni * sizeof(BvhNode)));
+  size_t sort_bytes = 0, scan_bytes = 0;
+  CU(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, codes[0], codes[1], ids[0], ids[1], (int)n, 0, 30, s));
+  CU(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, flags, scan, (int)n, s));
+  void *cub_tmp = nullptr;
+  CU(tmp.alloc(&cub_tmp, std::max(sort_bytes, scan_bytes)));
+  CU(cudaMemcpyAsync(d_boxes, fs.boxes.data(), n * sizeof(Box), cudaMemcpyHostToDevice, s));
+  c->scene_h2d_bytes += (double)n * sizeof(Box);
+  CU(cudaEventRecord(c->ev0, s));
+  const int g = (int)((n + 255) / 256);
+  k_lbvh_init<<<1, 1, 0, s>>>(st);
+  k_lbvh_bounds<<<std::min(g, c->sm_count * 8), 256, 0, s>>>(d_boxes, n, st);
+  k_lbvh_morton<<<g, 256, 0, s>>>(d_boxes, n, st, codes[0], ids[0]);
+  CU(cub::DeviceRadixSort::SortPairs(cub_tmp, sort_bytes, codes[0], codes[1], ids[0], ids[1], (int)n, 0, 30, s));
+  k_ploc_init<<<g, 256, 0, s>>>(d_boxes, ids[1], n, cl[0], st);
+  uint32_t m = n, node_base = 0;
+  int cur = 0, rounds = 0;
+  const char *env_radius = std::getenv("B200RT_PLOC_RADIUS"); // experiments only
+  const int radius = env_radius && std::atoi(env_radius) > 0 ? std::atoi(env_radius) : B200_PLOC_RADIUS;
+  while (m > 1) {
+    if (++rounds > 4096) return fail(B200RT_ERR_UNSUPPORTED, "device PLOC build: %u clusters left after %d rounds", m, rounds - 1);
+    const int gm = (int)((m + 255) / 256);
+    k_ploc_nearest<<<gm, 256, 0, s>>>(cl[cur], (int)m, radius, nn);
+    k_ploc_flag<<<gm, 256, 0, s>>>(nn, (int)m, flags);
+    CU(cub::DeviceScan::ExclusiveSum(cub_tmp, scan_bytes, flags, scan, (int)m, s));
+    k_ploc_merge<<<gm, 256, 0, s>>>(cl[cur], nn, flags, scan, (int)m, node_base, cl[cur ^ 1], nodes, totals);
+    unsigned int h[2] = {0, 0};
+    CU(cudaMemcpyAsync(h, totals, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    if (h[1] == 0 || h[0] + h[1] != m) return fail(B200RT_ERR_CUDA, "device PLOC build: round %d kept %u and merged %u of %u clusters", rounds, h[0], h[1], m);
+    m = h[0], node_base += h[1], cur ^= 1;
+  }
+  CU(cudaEventRecord(c->ev1, s));
+  CU(cudaGetLastError());
+  if (node_base != ni) return fail(B200RT_ERR_CUDA, "device PLOC build: %u nodes for %u primitives", node_base, n);
+  std::vector<BvhNode> topo(ni);
+  std::vector<uint32_t> sorted(n);
+  LbvhStats h;
+  CU(cudaMemcpyAsync(topo.data(), nodes, ni * sizeof(BvhNode), cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(sorted.data(), ids[1], n * 4, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(&h, st, sizeof h, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+  double bound[3];
+  for (int k = 0; k < 3; k++) {
+    float f;
+    std::memcpy(&f, &h.plane_max[k], 4);
+    bound[k] = (double)f;
+  }
+  out = finish_tree(topo, n, max_leaf, bound);
+  for (uint32_t &p : out.perm) p = sorted[p]; // leaf order -> Morton position -> flattener's entry order
+  out.build_ms += ms;                         // device clustering + host finishing pass (the copies in between are not in either)
+  return B200RT_OK;
+}
+
 int validate(const b200rt_scene_desc *d) {
   if (!d) return fail(B200RT_ERR_INVALID, "scene description is NULL");
   if (d->abi_version != B200RT_ABI_VERSION) return fail(B200RT_ERR_INVALID, "scene description has ABI version %u, library has %d", d->abi_version, B200RT_ABI_VERSION);
@@ -388,7 +474,8 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     c->bvh_width = (int)value; // takes effect at the next b200rt_upload_scene
     return B200RT_OK;
   case B200RT_OPT_BVH_BUILDER:
-    if (value != B200RT_BVH_HOST_SAH && value != B200RT_BVH_DEVICE_LBVH) return fail(B200RT_ERR_INVALID, "BVH builder must be 0 (host SAH) or 1 (device LBVH)");
+    if (value != B200RT_BVH_HOST_SAH && value != B200RT_BVH_DEVICE_LBVH && value != B200RT_BVH_DEVICE_PLOC)
+      return fail(B200RT_ERR_INVALID, "BVH builder must be 0 (host SAH), 1 (device LBVH) or 2 (device PLOC)");
     c->bvh_builder = (int)value; // takes effect at the next b200rt_upload_scene
     return B200RT_OK;
   case B200RT_OPT_TAIL_PATHS:
@@ -472,7 +559,16 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
         return fail(B200RT_ERR_UNSUPPORTED, "primitive %d has no material (the reference would dereference a null pointer)", e.prim);
     }
     if (!(use_device_builder = c->bvh_builder == B200RT_BVH_DEVICE_LBVH && !fs.boxes.empty())) {
-      bvh = BvhBuilder(fs.boxes, c->bvh_leaf ? c->bvh_leaf : (fs.boxes.size() <= 8192 ? 1 : 2)).run();
+      const int max_leaf = c->bvh_leaf ? c->bvh_leaf : (fs.boxes.size() <= 8192 ? 1 : 2);
+      bool built = false;
+      if (c->bvh_builder == B200RT_BVH_DEVICE_PLOC && !fs.boxes.empty()) {
+        const int prc = build_bvh_ploc(c, fs, max_leaf, bvh);
+        if (prc != B200RT_OK && prc != B200RT_ERR_UNSUPPORTED) return prc;
+        built = prc == B200RT_OK && bvh.max_depth <= B200_STACK; // a degenerate clustering (too deep, no convergence): host builder
+      }
+      // experiments: B200RT_SAH_PEEL=0 switches the largest-primitive candidate off, B200RT_SAH_SWEEP=1 the exact sweep on small nodes on
+      auto env_is = [](const char *name, int dflt) { const char *v = std::getenv(name); return (v ? std::atoi(v) : dflt) != 0; };
+      if (!built) bvh = BvhBuilder(fs.boxes, max_leaf, env_is("B200RT_SAH_PEEL", 1), env_is("B200RT_SAH_SWEEP", 0)).run();
       ordered.resize(fs.entries.size());
       for (size_t k = 0; k < ordered.size(); k++) ordered[k] = fs.entries[bvh.perm[k]];
       // node_step pushes at most one reference per level: a tree deeper than the traversal stack would drop subtrees silently

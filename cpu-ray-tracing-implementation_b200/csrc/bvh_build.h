@@ -8,6 +8,7 @@
 #pragma once
 #include <chrono>
 #include <numeric>
+#include <stdexcept>
 
 #include "flatten.h"
 
@@ -24,7 +25,8 @@ struct BuiltBvh {
 
 class BvhBuilder {
 public:
-  BvhBuilder(const std::vector<Box> &boxes, int max_leaf) : boxes_(boxes), max_leaf_(std::max(1, std::min(8, max_leaf))) {}
+  BvhBuilder(const std::vector<Box> &boxes, int max_leaf, bool peel = true, bool sweep = false)
+      : boxes_(boxes), max_leaf_(std::max(1, std::min(8, max_leaf))), peel_(peel), sweep_(sweep) {}
 
   BuiltBvh run() {
     auto t0 = std::chrono::steady_clock::now();
@@ -32,11 +34,15 @@ public:
     out_.perm.resize(n);
     std::iota(out_.perm.begin(), out_.perm.end(), 0u);
     cent_.resize(n * 3);
-    for (size_t i = 0; i < n; i++)
+    area_.resize(n);
+    for (size_t i = 0; i < n; i++) {
       for (int k = 0; k < 3; k++) {
         double c = 0.5 * (boxes_[i].lo[k] + boxes_[i].hi[k]);
         cent_[3 * i + k] = std::isfinite(c) ? c : 0.0;
       }
+      const double a = boxes_[i].area();
+      area_[i] = std::isfinite(a) ? a : 1e300;
+    }
     if (n > 0) {
       Box rb;
       out_.root = build(0, (uint32_t)n, 1, rb);
@@ -49,9 +55,11 @@ public:
 
 private:
   static constexpr int kBins = 16;
+  static constexpr uint32_t kSweep = 32;
   const std::vector<Box> &boxes_;
   int max_leaf_;
-  std::vector<double> cent_;
+  bool peel_, sweep_;
+  std::vector<double> cent_, area_;
   BuiltBvh out_;
   double cost_acc_ = 0, root_area_ = 0;
 
@@ -88,10 +96,13 @@ private:
     bounds.reset();
     Box cb;
     cb.reset();
+    uint32_t big = begin; // the primitive with the largest box (the peel-off candidate below)
+    double big_area = -1;
     for (uint32_t i = begin; i < end; i++) {
       const uint32_t id = out_.perm[i];
       bounds.add(boxes_[id]);
       cb.add(&cent_[3 * id]);
+      if (area_[id] > big_area) big_area = area_[id], big = i;
     }
     if (count == 1) return make_leaf(begin, end, depth, bounds);
 
@@ -138,16 +149,64 @@ private:
         }
       }
     }
+    // Small nodes, optional: the exact sweep over every split of the centroid order on every axis instead of the 16 bins.  Measured
+    // (profiles/r02_ar_sah_sweep.jsonl): +50 % build time, traversal within noise on all five configs, so it is off.
+    int sweep_axis = -1;
+    uint32_t sweep_left = 0;
+    if (sweep_ && depth < 40 && count <= kSweep) {
+      uint32_t order[kSweep];
+      double right_area[kSweep];
+      for (int axis = 0; axis < 3; axis++) {
+        for (uint32_t i = 0; i < count; i++) order[i] = out_.perm[begin + i];
+        std::stable_sort(order, order + count, [&](uint32_t a, uint32_t b) { return cent_[3 * a + axis] < cent_[3 * b + axis]; });
+        Box acc;
+        acc.reset();
+        for (uint32_t i = count - 1; i > 0; i--) {
+          acc.add(boxes_[order[i]]);
+          const double a = acc.area();
+          right_area[i] = std::isfinite(a) ? a : 1e300;
+        }
+        acc.reset();
+        for (uint32_t i = 0; i + 1 < count; i++) {
+          acc.add(boxes_[order[i]]);
+          double la = acc.area();
+          if (!std::isfinite(la)) la = 1e300;
+          const double cost = la * (i + 1) + right_area[i + 1] * (count - i - 1);
+          if (cost < best_cost) best_cost = cost, sweep_axis = axis, sweep_left = i + 1;
+        }
+      }
+    }
+    // One more candidate that centroid bins cannot express: the primitive with the largest box on its own against all the others.
+    // A primitive that spans the node (a fog boundary, a ground sphere, a wall) otherwise follows the centroid splits downwards and
+    // makes every node on its way as large as itself.  Measured (profiles/r02_aq_sah_peel_ploc_radius.jsonl): RTNW's tree cost 7.43 ->
+    // 2.66 and its frame +17.7 % (3 188 -> 3 754 Mrays/s); the other configs unchanged.
+    int32_t peel = -1;
+    if (peel_ && depth < 40 && count > 2 && big_area >= 0.25 * bounds.area()) { // (a mesh triangle never gets here: no second pass for it)
+      Box rest;
+      rest.reset();
+      for (uint32_t i = begin; i < end; i++)
+        if (i != big) rest.add(boxes_[out_.perm[i]]);
+      double ra = rest.area();
+      if (!std::isfinite(ra)) ra = 1e300;
+      const double cost = big_area + ra * (count - 1);
+      if (cost < best_cost) best_cost = cost, peel = (int32_t)big;
+    }
     double parent_area = bounds.area();
     if (!std::isfinite(parent_area)) parent_area = 1e300;
     if (count <= (uint32_t)max_leaf_) {
       // leaf cost: count intersections; split cost: one node (two boxes, ~1.2 intersections' worth) + children
       const double leaf_cost = (double)count * parent_area;
-      const double split_cost = best_axis < 0 ? INFINITY : 1.2 * parent_area + best_cost;
+      const double split_cost = (best_axis < 0 && peel < 0 && sweep_axis < 0) ? INFINITY : 1.2 * parent_area + best_cost;
       if (leaf_cost <= split_cost) return make_leaf(begin, end, depth, bounds);
     }
     uint32_t mid;
-    if (best_axis >= 0) {
+    if (peel >= 0) {
+      std::swap(out_.perm[begin], out_.perm[peel]);
+      mid = begin + 1;
+    } else if (sweep_axis >= 0) {
+      std::stable_sort(out_.perm.begin() + begin, out_.perm.begin() + end, [&](uint32_t a, uint32_t b) { return cent_[3 * a + sweep_axis] < cent_[3 * b + sweep_axis]; });
+      mid = begin + sweep_left;
+    } else if (best_axis >= 0) {
       const double lo = cb.lo[best_axis], scale = kBins / (cb.hi[best_axis] - cb.lo[best_axis]);
       auto it = std::partition(out_.perm.begin() + begin, out_.perm.begin() + end, [&](uint32_t id) {
         int b = (int)((cent_[3 * id + best_axis] - lo) * scale);
@@ -181,6 +240,116 @@ private:
     return (int32_t)me;
   }
 };
+
+// Host pass over a BVH2 TOPOLOGY that came from somewhere else (the device PLOC build, bvh_ploc.cuh): `in` holds one-primitive
+// leaves (reference ~(position << 3)) and inner nodes whose children always precede them, the root last.  Produces what
+// BvhBuilder::run() produces: leaves of up to max_leaf entries where the SAH rule of the host builder prefers a leaf to a split
+// (count * A <= 1.2 * A + sum of child costs), nodes in depth-first order, perm[k] = input position of the k-th entry in leaf order.
+inline BuiltBvh finish_tree(const std::vector<BvhNode> &in, uint32_t n_prims, int max_leaf, const double bound[3]) {
+  auto t0 = std::chrono::steady_clock::now();
+  BuiltBvh out;
+  max_leaf = std::max(1, std::min(8, max_leaf));
+  for (int k = 0; k < 3; k++) out.bound[k] = bound[k];
+  out.perm.reserve(n_prims);
+  if (n_prims == 0) return out;
+  if (in.empty()) { // one primitive: the leaf is the root
+    out.perm.push_back(0);
+    out.root = ~(int32_t)0;
+    out.n_leaves = 1, out.max_depth = 1, out.sah_cost = 1;
+    return out;
+  }
+  auto area = [](const float *b) {
+    const double dx = (double)b[1] - b[0], dy = (double)b[3] - b[2], dz = (double)b[5] - b[4];
+    if (!(dx >= 0 && dy >= 0 && dz >= 0)) return 0.0;
+    const double a = 2 * (dx * dy + dy * dz + dz * dx);
+    return std::isfinite(a) ? a : 1e300;
+  };
+  auto union_area = [&](const BvhNode &nd) {
+    float u[6];
+    for (int k = 0; k < 3; k++) u[2 * k] = std::min(nd.lbox[2 * k], nd.rbox[2 * k]), u[2 * k + 1] = std::max(nd.lbox[2 * k + 1], nd.rbox[2 * k + 1]);
+    return area(u);
+  };
+  // pass 1 (children precede parents): how many primitives a node holds if it becomes a leaf, 0 if it stays an inner node
+  const size_t nn = in.size();
+  std::vector<uint8_t> leaf_count(nn, 0);
+  auto count_of = [&](int32_t ref) -> uint32_t { return ref < 0 ? (((uint32_t)~ref) & 7u) + 1u : leaf_count[ref]; };
+  for (size_t i = 0; i < nn; i++) {
+    const BvhNode &nd = in[i];
+    if ((nd.left >= 0 && (size_t)nd.left >= i) || (nd.right >= 0 && (size_t)nd.right >= i)) throw std::runtime_error("finish_tree: a child does not precede its parent");
+    const uint32_t cl = count_of(nd.left), cr = count_of(nd.right);
+    if (cl == 0 || cr == 0 || cl + cr > (uint32_t)max_leaf) continue;
+    const double A = union_area(nd), la = area(nd.lbox), ra = area(nd.rbox);
+    if ((double)(cl + cr) * A <= 1.2 * A + la * cl + ra * cr) leaf_count[i] = (uint8_t)(cl + cr);
+  }
+  // pass 2: depth-first emission from the root (the last node)
+  struct Job {
+    int32_t node;  // input index
+    int32_t slot;  // output index, already reserved
+    uint32_t depth;
+  };
+  auto emit_leaf = [&](int32_t ref, uint32_t depth, double a) -> int32_t { // ref: an input leaf or an input node with leaf_count > 0
+    const uint32_t begin = (uint32_t)out.perm.size();
+    std::vector<int32_t> todo{ref};
+    while (!todo.empty()) {
+      const int32_t r = todo.back();
+      todo.pop_back();
+      if (r < 0)
+        out.perm.push_back(((uint32_t)~r) >> 3);
+      else
+        todo.push_back(in[r].right), todo.push_back(in[r].left);
+    }
+    const uint32_t count = (uint32_t)out.perm.size() - begin;
+    out.n_leaves++;
+    out.max_depth = std::max(out.max_depth, depth);
+    out.sah_cost += a * count;
+    return ~(int32_t)((begin << 3) | (count - 1));
+  };
+  const int32_t root = (int32_t)nn - 1;
+  if (leaf_count[root]) { // the whole scene fits one leaf
+    out.root = emit_leaf(root, 1, union_area(in[root]));
+    out.sah_cost = (double)leaf_count[root];
+    return out;
+  }
+  std::vector<Job> stack;
+  out.nodes.reserve(nn);
+  out.nodes.emplace_back();
+  stack.push_back({root, 0, 1});
+  const double root_area = union_area(in[root]);
+  while (!stack.empty()) {
+    const Job j = stack.back();
+    stack.pop_back();
+    BvhNode nd = in[j.node];
+    out.sah_cost += 1.2 * union_area(nd);
+    const int32_t kids[2] = {nd.left, nd.right};
+    int32_t refs[2];
+    int32_t pending[2] = {-1, -1};
+    // the left subtree follows its parent immediately (depth-first), so its slot is only known once it is emitted: reserve lazily
+    for (int k = 0; k < 2; k++) {
+      if (kids[k] < 0 || leaf_count[kids[k]]) {
+        refs[k] = 0; // filled below, in child order, so that leaf entries appear left to right
+        pending[k] = -2;
+      }
+    }
+    // leaves first in child order, then inner children get their slots (right pushed first so that left is processed next)
+    for (int k = 0; k < 2; k++)
+      if (pending[k] == -2) refs[k] = emit_leaf(kids[k], j.depth + 1, area(k == 0 ? nd.lbox : nd.rbox));
+    for (int k = 0; k < 2; k++)
+      if (pending[k] != -2) {
+        refs[k] = (int32_t)out.nodes.size();
+        out.nodes.emplace_back();
+      }
+    if (pending[1] != -2) stack.push_back({kids[1], refs[1], j.depth + 1});
+    if (pending[0] != -2) stack.push_back({kids[0], refs[0], j.depth + 1});
+    nd.left = refs[0], nd.right = refs[1];
+    nd.pad[0] = nd.pad[1] = 0;
+    out.nodes[j.slot] = nd;
+    out.max_depth = std::max(out.max_depth, j.depth);
+  }
+  out.root = 0;
+  if (root_area > 0) out.sah_cost /= root_area;
+  out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  return out;
+}
 
 // BVH2 -> BVH4: every kept node adopts its grandchildren, largest box first, until it has four children or only leaves.
 // Child references keep their encoding (inner: index into the NEW array; leaf: unchanged).

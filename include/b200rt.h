@@ -232,7 +232,7 @@ typedef enum b200rt_option {
   B200RT_OPT_FUSE_MISS = 8,     /* 1 (default): in a scene without background the extend kernel finishes a miss itself (it adds 0) instead of queueing the path */
   B200RT_OPT_EXTEND_STAGES = 9, /* tuning: ray batches staged in shared memory per warp, 2 (default) or 1; lane refill always uses 2 */
   B200RT_OPT_SMEM_CARVEOUT = 10, /* tuning: shared-memory carve-out of the extend kernel in percent, -1 (default) = smallest that fits */
-  B200RT_OPT_BVH_BUILDER = 11,  /* who builds the compacted BVH that replaces bvh_node's constructor (src/bvh_node.h:18-47): B200RT_BVH_HOST_SAH (default) or B200RT_BVH_DEVICE_LBVH */
+  B200RT_OPT_BVH_BUILDER = 11,  /* who builds the compacted BVH that replaces bvh_node's constructor (src/bvh_node.h:18-47): B200RT_BVH_HOST_SAH (default), B200RT_BVH_DEVICE_LBVH or B200RT_BVH_DEVICE_PLOC */
   B200RT_OPT_BVH_WIDTH = 12,    /* children per node of the traversed tree: 2, 4 (collapsed from the host SAH BVH2), 0 (default) = 4 above 2048 primitives */
   B200RT_OPT_PIPELINES = 13,    /* 1 or 2 (default): with 2 the sample range is split into two independent wavefronts on two streams; each half's kernels fill the SMs the other half's kernel has drained */
   B200RT_OPT_PIPE_EXTEND_CTAS = 14, /* tuning: resident extend CTAs per SM in two-pipeline mode (1..4, default 4; fewer leave registers for the other half's kernels and were measured slower) */
@@ -260,6 +260,7 @@ typedef enum b200rt_option {
 
 #define B200RT_BVH_HOST_SAH 0    /* binned SAH over three axes on the host: best tree, ~0.5 us per primitive */
 #define B200RT_BVH_DEVICE_LBVH 1 /* Morton-order linear BVH built by CUDA kernels: one primitive per leaf, lower quality, ~1000x faster to build */
+#define B200RT_BVH_DEVICE_PLOC 2 /* topology by parallel locally-ordered clustering on the device (csrc/bvh_ploc.cuh), leaf pairs + layout + BVH4 collapse on the host: close to the SAH tree's traversal speed at a fraction of its build time */
 #define B200RT_TRAVERSAL_FAST 0
 #define B200RT_TRAVERSAL_MIRROR 1
 

@@ -28,7 +28,73 @@ void *emu_scene_create(const b200rt_scene_desc *d, int leaf_size) {
     Flattener fl(*d);
     fl.run();
     e->fs = std::move(fl.out);
-    e->bvh = BvhBuilder(e->fs.boxes, leaf_size).run();
+    if (leaf_size >= 0) {
+      e->bvh = BvhBuilder(e->fs.boxes, leaf_size).run();
+    } else {
+      // the device PLOC build (csrc/bvh_ploc.cuh) restated serially: clusters in flattener order (the device sorts by Morton code
+      // first; any order gives a valid tree), rounds of mutual nearest neighbours within +-radius, children before parents, the
+      // root last; then the host pass the library runs on the device's topology (bvh_build.h:finish_tree), which is what this
+      // mode is for.  -leaf_size = primitives per leaf.
+      struct Cl {
+        float v[6];
+        int32_t ref;
+      };
+      const std::vector<Box> &bx = e->fs.boxes;
+      std::vector<Cl> cl(bx.size());
+      double bound[3] = {0, 0, 0};
+      for (size_t i = 0; i < bx.size(); i++) {
+        for (int k = 0; k < 3; k++) {
+          float lo = (float)bx[i].lo[k], hi = (float)bx[i].hi[k];
+          if ((double)lo > bx[i].lo[k]) lo = std::nextafterf(lo, -INFINITY);
+          if ((double)hi < bx[i].hi[k]) hi = std::nextafterf(hi, INFINITY);
+          cl[i].v[2 * k] = lo, cl[i].v[2 * k + 1] = hi;
+          for (float f : {lo, hi})
+            if (std::isfinite(f) && std::fabs((double)f) > bound[k]) bound[k] = std::fabs((double)f);
+        }
+        cl[i].ref = ~(int32_t)((uint32_t)i << 3);
+      }
+      auto union_area = [](const Cl &a, const Cl &b) {
+        double d[3];
+        for (int k = 0; k < 3; k++) d[k] = (double)std::max(a.v[2 * k + 1], b.v[2 * k + 1]) - (double)std::min(a.v[2 * k], b.v[2 * k]);
+        if (!(d[0] >= 0 && d[1] >= 0 && d[2] >= 0)) return 0.0;
+        const double ar = 2 * (d[0] * d[1] + d[1] * d[2] + d[2] * d[0]);
+        return std::isfinite(ar) ? ar : 1e300;
+      };
+      std::vector<BvhNode> topo;
+      const int radius = 4;
+      while (cl.size() > 1) {
+        const int m = (int)cl.size();
+        std::vector<int> nn(m, -1);
+        for (int i = 0; i < m; i++) {
+          double best = 0;
+          for (int j = std::max(0, i - radius); j <= std::min(m - 1, i + radius); j++) {
+            if (j == i) continue;
+            const double ar = union_area(cl[i], cl[j]);
+            if (nn[i] < 0 || ar < best) best = ar, nn[i] = j;
+          }
+        }
+        std::vector<Cl> next;
+        for (int i = 0; i < m; i++) {
+          const int j = nn[i];
+          const bool mutual = nn[j] == i;
+          if (mutual && i > j) continue;
+          Cl c = cl[i];
+          if (mutual) {
+            BvhNode nd;
+            std::memset(&nd, 0, sizeof nd);
+            for (int k = 0; k < 6; k++) nd.lbox[k] = cl[i].v[k], nd.rbox[k] = cl[j].v[k];
+            nd.left = cl[i].ref, nd.right = cl[j].ref;
+            for (int k = 0; k < 3; k++) c.v[2 * k] = std::min(c.v[2 * k], cl[j].v[2 * k]), c.v[2 * k + 1] = std::max(c.v[2 * k + 1], cl[j].v[2 * k + 1]);
+            c.ref = (int32_t)topo.size();
+            topo.push_back(nd);
+          }
+          next.push_back(c);
+        }
+        if (next.size() == cl.size()) throw std::runtime_error("no mutual pair");
+        cl.swap(next);
+      }
+      e->bvh = finish_tree(topo, (uint32_t)bx.size(), -leaf_size, bound);
+    }
   } catch (const std::exception &ex) {
     delete e;
     return nullptr;

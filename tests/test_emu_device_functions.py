@@ -29,6 +29,27 @@ def test_emu_hits_vs_reference_golden(emu_lib, name, leaf):
         assert ok.all(), f"{name}: {k} differs on {(~ok).sum()} of {keep.sum()} rays"
 
 
+@pytest.mark.parametrize("leaf", [1, 2, 3])
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_emu_clustered_tree_through_finish_tree(emu_lib, name, leaf):
+    """The host pass the library runs on the device PLOC topology (csrc/bvh_build.h: finish_tree: leaf merging by the SAH rule,
+    depth-first layout, entry permutation) on a serial restatement of the clustering (tests/emu/emu.cc): a different tree again,
+    the same records as the reference."""
+    g = golden(name)
+    es = emu_lib.EmuScene(g.scene, leaf_size=-leaf)
+    info, host = es.info(), emu_lib.EmuScene(g.scene, leaf_size=leaf).info()
+    assert info["entries"] == host["entries"] and -(-info["entries"] // leaf) <= info["leaves"] <= info["entries"]
+    assert info["bvh_nodes"] == max(0, info["leaves"] - 1) and 1 <= info["bvh_depth"] <= 64
+    out = es.trace(g["trace_rays"], seed=99)
+    keep = np.ones(len(out["prim"]), bool)
+    if name in VOLUME_SCENES:
+        vol = np.array(sorted(g.volume_prims()))
+        keep = ~np.isin(out["prim"], vol) & ~np.isin(g["trace_prim"], vol)
+    for k in ("prim", "front", "t", "p", "normal", "uv"):
+        ok = same(out[k][keep], g["trace_" + k][keep])
+        assert ok.all(), f"{name}: {k} differs on {(~ok).sum()} of {keep.sum()} rays"
+
+
 @pytest.mark.parametrize("name", ["cornell", "rtow", "fox", "rtnw"])
 def test_emu_mirror_equals_fast(emu_lib, name):
     g = golden(name)

@@ -410,16 +410,23 @@ def test_sponza_standin_hits(ctx, build_oracle):
     assert np.isfinite(img).all() and st["rays"] > st["samples"]
 
 
+@pytest.mark.parametrize("builder", [abi.BVH_DEVICE_LBVH, abi.BVH_DEVICE_PLOC])
 @pytest.mark.parametrize("name", ALL_SCENES)
-def test_device_built_bvh_gives_the_same_hits(name):
-    """B200RT_OPT_BVH_BUILDER = DEVICE_LBVH (csrc/bvh_gpu.cuh): a different tree, the same records as the reference."""
+def test_device_built_bvh_gives_the_same_hits(name, builder):
+    """B200RT_OPT_BVH_BUILDER = DEVICE_LBVH (csrc/bvh_gpu.cuh) / DEVICE_PLOC (csrc/bvh_ploc.cuh + finish_tree): a different tree,
+    the same records as the reference."""
     g = golden(name)
     c = pkg.backend.Context(0)
     try:
-        c.set_option(abi.OPT_BVH_BUILDER, abi.BVH_DEVICE_LBVH)
+        c.set_option(abi.OPT_BVH_BUILDER, builder)
+        if builder == abi.BVH_DEVICE_PLOC:
+            c.set_option(abi.OPT_BVH_LEAF_SIZE, 2)  # small scenes default to one primitive per leaf: exercise the leaf-pair pass
         c.upload_scene(g.scene)
         info = c.bvh_info()
-        assert info["n_leaves"] == info["n_prims"] and info["n_nodes"] == max(0, info["n_prims"] - 1)
+        if builder == abi.BVH_DEVICE_LBVH:
+            assert info["n_leaves"] == info["n_prims"] and info["n_nodes"] == max(0, info["n_prims"] - 1)
+        else:
+            assert info["n_prims"] / 2 <= info["n_leaves"] <= info["n_prims"]
         assert 1 <= info["max_depth"] <= 64
         out = c.trace(g["trace_rays"], seed=99)
         ref = {k: g["trace_" + k] for k in ("prim", "t", "uv", "front", "p", "normal")}
@@ -459,6 +466,15 @@ def test_device_built_bvh_sponza_standin():
             assert same(host[k], dev[k]).all(), k
         assert dinfo["n_prims"] == hinfo["n_prims"] and dinfo["build_ms"] < hinfo["build_ms"]
         print(f"sponza stand-in BVH: host SAH {hinfo['build_ms']:.1f} ms (cost {hinfo['sah_cost']:.1f}), device LBVH {dinfo['build_ms']:.2f} ms (cost {dinfo['sah_cost']:.1f}, depth {dinfo['max_depth']})")
+        c.set_option(abi.OPT_BVH_BUILDER, abi.BVH_DEVICE_PLOC)
+        c.upload_scene(sc)
+        ploc = c.trace(rays)
+        pinfo = c.bvh_info()
+        for k in ("prim", "front", "t", "p", "normal"):
+            assert same(host[k], ploc[k]).all(), k
+        assert pinfo["n_prims"] == hinfo["n_prims"] and pinfo["build_ms"] < hinfo["build_ms"]
+        assert pinfo["n_leaves"] < pinfo["n_prims"]  # leaf pairs were formed
+        print(f"                     device PLOC + host finish {pinfo['build_ms']:.2f} ms (cost {pinfo['sah_cost']:.1f}, depth {pinfo['max_depth']}, {pinfo['n_nodes']} BVH4 nodes vs {hinfo['n_nodes']})")
     finally:
         c.close()
 
@@ -533,7 +549,7 @@ def _empty_world(g):
     return s
 
 
-@pytest.mark.parametrize("builder", [abi.BVH_HOST_SAH, abi.BVH_DEVICE_LBVH])
+@pytest.mark.parametrize("builder", [abi.BVH_HOST_SAH, abi.BVH_DEVICE_LBVH, abi.BVH_DEVICE_PLOC])
 @pytest.mark.parametrize("width", [2, 4])
 def test_edge_cases_empty_and_single_primitive_worlds(builder, width, build_oracle):
     """Empty world: every ray misses, every sample is the background (here solid white: sum == spp).  One-primitive world:

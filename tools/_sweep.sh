@@ -1,6 +1,6 @@
-# scratch: BVH4 extend kernel at 20 / 24 warps per SM (B200RT_OPT_EXTEND_BLOCKS = 5 / 6) against the 16-warp default
+# scratch: host SAH: exact sweep on small nodes on / off (largest-primitive candidate on)
 mkdir -p gpurun_out
-for rep in 1 2; do for o in "" "--opt 6=5" "--opt 6=6"; do
-  python tools/bench_scenes.py --scenes rtnw,sponza --reps 3 $o 2>&1 >> gpurun_out/r02an_bvh4_occupancy.jsonl
+for rep in 1 2; do for p in 0 1; do
+  B200RT_SAH_SWEEP=$p python tools/bench_scenes.py --scenes sponza,rtnw,fox,rtow,cornell --reps 2 --builder 0 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"sweep=$p\"]/" >> gpurun_out/r02ar_sah_sweep.jsonl
 done; done
-grep -o '"scene": "[a-z]*", "opts": [^]]*]\|"mrays_per_s": [0-9.]*' gpurun_out/r02an_bvh4_occupancy.jsonl | paste - -
+grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*\|"build_ms": [0-9.]*\|"sah_cost": [0-9.]*' gpurun_out/r02ar_sah_sweep.jsonl | paste - - - - -

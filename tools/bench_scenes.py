@@ -72,7 +72,7 @@ def main():
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--full", action="store_true", help="time every config at its full spp (C5 alone is 34 G samples: about a minute on one B200)")
     ap.add_argument("--cpu", action="store_true", help="add the CPU baseline of every scene (see cpu_baseline)")
-    ap.add_argument("--builder", type=int, default=0, help="0 = host SAH BVH (default), 1 = device LBVH (csrc/bvh_gpu.cuh)")
+    ap.add_argument("--builder", type=int, default=0, help="0 = host SAH BVH (default), 1 = device LBVH (csrc/bvh_gpu.cuh), 2 = device PLOC + host finishing pass (csrc/bvh_ploc.cuh)")
     ap.add_argument("--width", type=int, default=0, help="BVH width: 0 = automatic, 2, 4")
     ap.add_argument("--pipelines", type=int, default=2, help="independent wavefronts on two streams (1 also reports the extend share)")
     ap.add_argument("--tail", type=int, default=-1, help="B200RT_OPT_TAIL_PATHS (-1 = library default, 0 = off)")
@@ -105,7 +105,7 @@ def main():
             _, st = ctx.render(1, 0, spp)
             if best is None or st["gpu_ms"] < best["gpu_ms"]:
                 best = st
-        line = {"scene": name, "opts": args.opt, "builder": "device LBVH" if args.builder else "host SAH", "config": CONFIGS[name], "width": cam.image_width, "height": cam.image_height, "spp_timed": spp,
+        line = {"scene": name, "opts": args.opt, "builder": ["host SAH", "device LBVH", "device PLOC"][args.builder], "config": CONFIGS[name], "width": cam.image_width, "height": cam.image_height, "spp_timed": spp,
                 "spp_config": cam.samples_per_pixel, "max_depth": cam.max_depth, "mrays_per_s": best["rays"] / best["gpu_ms"] / 1e3,
                 "msamples_per_s": best["samples"] / best["gpu_ms"] / 1e3, "rays_per_sample": best["rays"] / best["samples"],
                 "gpu_ms": best["gpu_ms"], "extend_share": (best["extend_ms"] / best["gpu_ms"]) if best["extend_ms"] > 0 else None, "waves": best["waves"],
