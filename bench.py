@@ -43,10 +43,10 @@ EXTEND_BYTES_PER_RAY = 128  # k_extend_persistent: reads 7 of the 8 path quads (
 #   traffic: dram__bytes_read.sum + dram__bytes_write.sum per ray of one full 16 Mi-ray launch
 #   issue_active: smsp__issue_active.avg.pct_of_peak_sustained_active / 100; threads_per_inst: smsp__thread_inst_executed_per_inst_executed.ratio
 NCU = {
-    # traffic from launch 0 (a full wave of camera rays: the ray count is known exactly), issue / lanes from launch 1 (a mid-path wave)
-    "rtow": {"traffic_bytes_per_ray": 2281.03e6 / 16200000, "issue_active": 0.62, "threads_per_inst": 16.4, "source": "profiles/r02_q_extend_rtow_launch{0,1}_ncu_full.txt"},
-    "rtnw": {"traffic_bytes_per_ray": 2258.26e6 / 16640000, "issue_active": 0.60, "threads_per_inst": 10.3, "source": "profiles/r02_q_extend_rtnw_launch{0,1}_ncu_full.txt (BVH4)"},
-    "sponza": {"traffic_bytes_per_ray": 2341.96e6 / 16588800, "issue_active": 0.51, "threads_per_inst": 11.5, "source": "profiles/r02_q_extend_sponza_launch{0,1}_ncu_full.txt (BVH4)"},
+    # traffic from launch 0 (a full wave of camera rays: the ray count is known exactly), issue / lanes from launch 1 (the first secondary wave)
+    "rtow": {"traffic_bytes_per_ray": 2279.28e6 / 16200000, "issue_active": 0.63, "threads_per_inst": 16.1, "source": "profiles/r02_as_extend_rtow_launch{0,1}_ncu_full.txt"},
+    "rtnw": {"traffic_bytes_per_ray": 2347.15e6 / 16640000, "issue_active": 0.61, "threads_per_inst": 12.2, "source": "profiles/r02_as_extend_rtnw_launch{0,1}_ncu_full.txt (BVH4)"},
+    "sponza": {"traffic_bytes_per_ray": 2340.10e6 / 16588800, "issue_active": 0.44, "threads_per_inst": 18.7, "source": "profiles/r02_as_extend_sponza_launch{0,1}_ncu_full.txt (BVH4, warp-uniform loop)"},
 }
 
 

@@ -140,8 +140,11 @@ struct b200rt_ctx {
   size_t l2_window_max = 0, l2_persist_max = 0;
   int ray_sort = 0;    // B200RT_OPT_RAY_SORT
   int octant_sort = 0; // B200RT_OPT_OCTANT_SORT
-  int extend_loop = 0; // B200RT_OPT_EXTEND_LOOP: 0 = while-while, 1 = warp-uniform threshold if-if
-  int leaf_lanes = 8;  // B200RT_OPT_LEAF_LANES
+  int extend_loop = -1; // B200RT_OPT_EXTEND_LOOP: 0 = while-while, 1 = warp-uniform threshold if-if, -1 = by scene (1 on triangle meshes)
+  int leaf_lanes = 0;   // B200RT_OPT_LEAF_LANES; 0 = 20 when the scene picked the loop, 8 when the caller did
+  bool mesh_scene = false; // a BVH4 whose leaves are almost all triangles (set by b200rt_upload_scene)
+  int loop_mode() const { return extend_loop >= 0 ? extend_loop : (mesh_scene ? 1 : 0); }
+  int loop_lanes() const { return leaf_lanes > 0 ? leaf_lanes : (extend_loop < 0 ? 20 : 8); }
   int wave_loop = 1; // B200RT_OPT_WAVE_LOOP: 1 = device-driven CUDA-graph while loop, 0 = host-driven loop with read-backs
   cudaEvent_t ev_fork = nullptr;
   int pipelines = 2;        // measured: +4 % on RTOW, +5 % on the Sponza stand-in over one pipeline (profiles/r01_r_pipelines.txt)
@@ -507,11 +510,11 @@ int b200rt_set_option(b200rt_ctx *c, int option, double value) {
     c->octant_sort = value != 0;
     return B200RT_OK;
   case B200RT_OPT_EXTEND_LOOP:
-    if (value != 0 && value != 1) return fail(B200RT_ERR_INVALID, "extend loop must be 0 (while-while) or 1 (warp-uniform)");
+    if (value != 0 && value != 1 && value != -1) return fail(B200RT_ERR_INVALID, "extend loop must be 0 (while-while), 1 (warp-uniform) or -1 (chosen by scene)");
     c->extend_loop = (int)value;
     return B200RT_OK;
   case B200RT_OPT_LEAF_LANES:
-    if (!(value >= 1 && value <= 32)) return fail(B200RT_ERR_INVALID, "leaf lanes must be in [1, 32]");
+    if (!(value >= 0 && value <= 32)) return fail(B200RT_ERR_INVALID, "leaf lanes must be in [1, 32] (0 = default)");
     c->leaf_lanes = (int)value;
     return B200RT_OK;
   case B200RT_OPT_WAVE_LOOP:
@@ -712,6 +715,11 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
   c->kinds_present = 0;
   for (uint32_t i = 0; i < d->n_materials; i++) c->kinds_present |= 1u << d->materials[i].kind;
   c->bg_mode = d->background_tex < 0 ? 1 : 0;
+  { // triangle meshes behind a BVH4 run the warp-uniform extend loop unless the caller says otherwise (B200RT_OPT_EXTEND_LOOP)
+    size_t n_tri_entries = 0;
+    for (const Entry &e : fs.entries) n_tri_entries += entry_kind(e) == E_TRI;
+    c->mesh_scene = S.bvh4 != nullptr && n_tri_entries * 10 >= fs.entries.size() * 9;
+  }
   c->scene_optins = d->tri_uv != nullptr;
   for (uint32_t i = 0; i < d->n_textures; i++) c->scene_optins |= d->textures[i].kind == B200RT_TEX_PICTURE_LINEAR;
   for (uint32_t i = 0; i < d->n_images; i++) c->scene_optins |= d->images[i].bytes_per_pixel >= 12;
@@ -1003,9 +1011,9 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
     case 106: launch_extend(k_extend_persistent<80, false, 4, 2, true>, c, w, 6, 128, 4 * 2 * 3584, s, cur, wp); break; // 24 warps per SM
 #endif
     default: // 128 registers, 4-warp CTAs
-      if (c->extend_loop == 1 && c->S.bvh4)
+      if (c->loop_mode() == 1 && c->S.bvh4)
         launch_extend(k_extend_persistent<128, false, 4, 2, true, true>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);
-      else if (c->extend_loop == 1)
+      else if (c->loop_mode() == 1)
         launch_extend(k_extend_persistent<128, false, 4, 2, false, true>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);
       else if (c->S.bvh4)
         launch_extend(k_extend_persistent<128, false, 4, 2, true>, c, w, ext_ctas, 128, 4 * 2 * 3584, s, cur, wp);
@@ -1153,7 +1161,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     q.max_depth = c->cam.max_depth;
     q.kill_zero = c->kill_zero;
     q.fused_miss = (mirror || !c->fuse_miss) ? 0 : c->bg_mode;
-    q.leaf_lanes = c->leaf_lanes;
+    q.leaf_lanes = c->loop_lanes();
     q.octant_sort = c->octant_sort;
     q.refill = c->refill_lanes ? c->refill_lanes : (c->S.n_bvh_nodes >= 32768 ? 8 : 32);
     for (int k = 0; k < 3; k++) q.bound[k] = c->S.bound[k];
@@ -1219,7 +1227,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
     for (int p = 0; p < n_pipe; p++) {
       std::string key;
       key_add(key, c->S), key_add(key, cam), key_add(key, wp[p]), key_add(key, cap[p]), key_add(key, d_rgb_sum), key_add(key, ext_ctas);
-      key_add(key, c->tail_paths), key_add(key, c->extend_blocks), key_add(key, c->speculative), key_add(key, c->extend_stages), key_add(key, c->carveout_pct), key_add(key, c->extend_loop), key_add(key, c->l2_persist), key_add(key, c->ray_sort);
+      key_add(key, c->tail_paths), key_add(key, c->extend_blocks), key_add(key, c->speculative), key_add(key, c->extend_stages), key_add(key, c->carveout_pct), key_add(key, c->loop_mode()), key_add(key, c->l2_persist), key_add(key, c->ray_sort);
       key_add(key, c->kinds_present), key_add(key, c->scene_optins), key_add(key, c->w[p].pools), key_add(key, c->w[p].hits);
       if ((rc = ensure_wave_graph(c, c->w[p], key, cam, wp[p], grid_for(c, cap[p], 256, 8), grid_for(c, cap[p], 128, 16), d_rgb_sum, ext_ctas)) != B200RT_OK) return rc;
       CU(cudaGraphLaunch(c->w[p].graph_exec, ps[p]));

@@ -244,8 +244,10 @@ typedef enum b200rt_option {
                                  b200rt_stats::extend_ms).  The mirror traversal always uses the host loop */
   B200RT_OPT_EXTEND_LOOP = 17, /* tuning: loop structure of the persistent extend kernel: 0 = while-while (inner nodes until every lane of the warp has
                                   found a leaf, then the leaves), 1 = warp-uniform "threshold if-if": the leaf phase starts as soon as
-                                  B200RT_OPT_LEAF_LANES lanes wait at a leaf */
-  B200RT_OPT_LEAF_LANES = 18,  /* tuning: see B200RT_OPT_EXTEND_LOOP (1..32, default 8; 32 = the while-while schedule) */
+                                  B200RT_OPT_LEAF_LANES lanes wait at a leaf; -1 (default) = by scene: 1 with 20 lanes for a triangle mesh behind
+                                  the BVH4 (>= 90 % of the leaves are triangles), 0 otherwise */
+  B200RT_OPT_LEAF_LANES = 18,  /* tuning: see B200RT_OPT_EXTEND_LOOP (1..32; 0 = default: 20 when the scene chose the loop, 8 when the caller did;
+                                  32 = the while-while schedule) */
   B200RT_OPT_L2_PERSIST = 19,  /* 1 (default): the tree, the leaf entries and the primitive rows are uploaded into one address range that the render
                                   kernels declare as a persisting L2 access-policy window (the wave's path state streams past it) */
   B200RT_OPT_TRI_F32 = 20,     /* 1 (default): triangle vertices are kept as 48-byte binary32 rows when every coordinate is exactly representable

@@ -286,8 +286,8 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
             ctx.set_option(abi.OPT_EXTEND_STAGES, 2)
             ctx.set_option(abi.OPT_SMEM_CARVEOUT, -1)
             ctx.set_option(abi.OPT_WAVE_LOOP, 1)
-            ctx.set_option(abi.OPT_EXTEND_LOOP, 0)
-            ctx.set_option(abi.OPT_LEAF_LANES, 8)
+            ctx.set_option(abi.OPT_EXTEND_LOOP, -1)
+            ctx.set_option(abi.OPT_LEAF_LANES, 0)
             ctx.set_option(abi.OPT_TRI_F32, 1)
             ctx.set_option(abi.OPT_L2_PERSIST, 1)
             if abi.OPT_BVH_WIDTH in opts or abi.OPT_TRI_F32 in opts:
@@ -305,8 +305,8 @@ def test_traversal_tuning_options_do_not_change_the_image(ctx, name):
         ctx.set_option(abi.OPT_EXTEND_STAGES, 2)
         ctx.set_option(abi.OPT_SMEM_CARVEOUT, -1)
         ctx.set_option(abi.OPT_WAVE_LOOP, 1)
-        ctx.set_option(abi.OPT_EXTEND_LOOP, 0)
-        ctx.set_option(abi.OPT_LEAF_LANES, 8)
+        ctx.set_option(abi.OPT_EXTEND_LOOP, -1)
+        ctx.set_option(abi.OPT_LEAF_LANES, 0)
         ctx.set_option(abi.OPT_BVH_WIDTH, 0)
 
 
