@@ -569,9 +569,10 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
         if (prc != B200RT_OK && prc != B200RT_ERR_UNSUPPORTED) return prc;
         built = prc == B200RT_OK && bvh.max_depth <= B200_STACK; // a degenerate clustering (too deep, no convergence): host builder
       }
-      // experiments: B200RT_SAH_PEEL=0 switches the largest-primitive candidate off, B200RT_SAH_SWEEP=1 the exact sweep on small nodes on
+      // experiments: B200RT_SAH_PEEL=0 switches the largest-primitive candidate off, B200RT_SAH_SWEEP=1 the exact sweep on small nodes on,
+      // B200RT_SAH_AREA=1 the box-area axis
       auto env_is = [](const char *name, int dflt) { const char *v = std::getenv(name); return (v ? std::atoi(v) : dflt) != 0; };
-      if (!built) bvh = BvhBuilder(fs.boxes, max_leaf, env_is("B200RT_SAH_PEEL", 1), env_is("B200RT_SAH_SWEEP", 0)).run();
+      if (!built) bvh = BvhBuilder(fs.boxes, max_leaf, env_is("B200RT_SAH_PEEL", 1), env_is("B200RT_SAH_SWEEP", 0), env_is("B200RT_SAH_AREA", 0)).run();
       ordered.resize(fs.entries.size());
       for (size_t k = 0; k < ordered.size(); k++) ordered[k] = fs.entries[bvh.perm[k]];
       // node_step pushes at most one reference per level: a tree deeper than the traversal stack would drop subtrees silently
@@ -994,7 +995,7 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
 #ifndef B200_BVH4_OCCUPANCY_EXPERIMENT
 #define B200_BVH4_OCCUPANCY_EXPERIMENT 0 // 1: B200RT_OPT_EXTEND_BLOCKS 5 / 6 also select 96- / 80-register BVH4 kernels (measured: slower)
 #endif
-    switch (c->S.bvh4 ? (B200_BVH4_OCCUPANCY_EXPERIMENT && (c->extend_blocks == 5 || c->extend_blocks == 6) ? 100 + c->extend_blocks : 0)
+    switch (c->S.bvh4 ? (B200_BVH4_OCCUPANCY_EXPERIMENT && c->extend_blocks >= 5 ? (c->loop_mode() == 1 ? 200 : 100) + c->extend_blocks : 0)
                       : c->extend_blocks * 2 + (c->speculative ? 1 : 0)) { // the other tuning variants walk the BVH2 only
     // EXTEND_BLOCKS names the resident WARPS per SM / 4; registers per thread follow (65536 / 32 / warps, multiple of 8)
 #define EXT(MAXREG, SPEC, WARPS, STAGES)                                                                               \
@@ -1009,6 +1010,11 @@ int launch_wave(b200rt_ctx *c, b200rt_ctx::WaveSet &w, cudaStream_t s, unsigned 
     // BVH4 at higher occupancy (latency-bound scenes: the Sponza stand-in waits on L2 with four warps per scheduler)
     case 105: launch_extend(k_extend_persistent<96, false, 4, 2, true>, c, w, 5, 128, 4 * 2 * 3584, s, cur, wp); break; // 20 warps per SM
     case 106: launch_extend(k_extend_persistent<80, false, 4, 2, true>, c, w, 6, 128, 4 * 2 * 3584, s, cur, wp); break; // 24 warps per SM
+    // the same under the warp-uniform loop, and with one staging buffer per warp (more of the 256 KB left as L1)
+    case 205: launch_extend(k_extend_persistent<96, false, 4, 2, true, true>, c, w, 5, 128, 4 * 2 * 3584, s, cur, wp); break;
+    case 206: launch_extend(k_extend_persistent<80, false, 4, 2, true, true>, c, w, 6, 128, 4 * 2 * 3584, s, cur, wp); break;
+    case 214: launch_extend(k_extend_persistent<128, false, 4, 1, true, true>, c, w, ext_ctas, 128, 4 * 1 * 3584, s, cur, wp); break;
+    case 215: launch_extend(k_extend_persistent<96, false, 4, 1, true, true>, c, w, 5, 128, 4 * 1 * 3584, s, cur, wp); break;
 #endif
     default: // 128 registers, 4-warp CTAs
       if (c->loop_mode() == 1 && c->S.bvh4)

@@ -7,6 +7,7 @@
 // change the answer: ties are resolved by Entry::order (flatten.h).
 #pragma once
 #include <chrono>
+#include <cmath>
 #include <numeric>
 #include <stdexcept>
 
@@ -25,8 +26,8 @@ struct BuiltBvh {
 
 class BvhBuilder {
 public:
-  BvhBuilder(const std::vector<Box> &boxes, int max_leaf, bool peel = true, bool sweep = false)
-      : boxes_(boxes), max_leaf_(std::max(1, std::min(8, max_leaf))), peel_(peel), sweep_(sweep) {}
+  BvhBuilder(const std::vector<Box> &boxes, int max_leaf, bool peel = true, bool sweep = false, bool area_axis = false)
+      : boxes_(boxes), max_leaf_(std::max(1, std::min(8, max_leaf))), peel_(peel), sweep_(sweep), area_axis_(area_axis) {}
 
   BuiltBvh run() {
     auto t0 = std::chrono::steady_clock::now();
@@ -35,6 +36,7 @@ public:
     std::iota(out_.perm.begin(), out_.perm.end(), 0u);
     cent_.resize(n * 3);
     area_.resize(n);
+    larea_.resize(n);
     for (size_t i = 0; i < n; i++) {
       for (int k = 0; k < 3; k++) {
         double c = 0.5 * (boxes_[i].lo[k] + boxes_[i].hi[k]);
@@ -42,6 +44,7 @@ public:
       }
       const double a = boxes_[i].area();
       area_[i] = std::isfinite(a) ? a : 1e300;
+      larea_[i] = area_[i] > 1e-300 ? std::log2(area_[i]) : -1000.0;
     }
     if (n > 0) {
       Box rb;
@@ -58,8 +61,9 @@ private:
   static constexpr uint32_t kSweep = 32;
   const std::vector<Box> &boxes_;
   int max_leaf_;
-  bool peel_, sweep_;
-  std::vector<double> cent_, area_;
+  bool peel_, sweep_, area_axis_;
+  std::vector<double> cent_, area_, larea_;
+  double key(uint32_t id, int axis) const { return axis < 3 ? cent_[3 * id + axis] : larea_[id]; } // axis 3: log2 of the box area
   BuiltBvh out_;
   double cost_acc_ = 0, root_area_ = 0;
 
@@ -97,12 +101,13 @@ private:
     Box cb;
     cb.reset();
     uint32_t big = begin; // the primitive with the largest box (the peel-off candidate below)
-    double big_area = -1;
+    double big_area = -1, alo = INFINITY, ahi = -INFINITY;
     for (uint32_t i = begin; i < end; i++) {
       const uint32_t id = out_.perm[i];
       bounds.add(boxes_[id]);
       cb.add(&cent_[3 * id]);
       if (area_[id] > big_area) big_area = area_[id], big = i;
+      alo = std::min(alo, larea_[id]), ahi = std::max(ahi, larea_[id]);
     }
     if (count == 1) return make_leaf(begin, end, depth, bounds);
 
@@ -110,16 +115,19 @@ private:
     double best_cost = INFINITY;
     int best_axis = -1, best_plane = -1;
     if (depth < 40) {
-      for (int axis = 0; axis < 3; axis++) {
-        const double lo = cb.lo[axis], ext = cb.hi[axis] - cb.lo[axis];
-        if (!(ext > 0) || !std::isfinite(ext)) continue;
+      // axes 0..2: centroid coordinates.  Axis 3 (optional): log2 of the box area, i.e. "the large primitives against the small ones", a
+      // partition no centroid plane expresses (walls around furniture); only where the areas in the node span more than a factor 4
+      // Measured (profiles/r02_aw_sah_area_axis.jsonl): Sponza stand-in +1.1 %, Cornell +0.9 %, RTNW -0.9 %, build time +8 %: off.
+      for (int axis = 0; axis < (area_axis_ ? 4 : 3); axis++) {
+        const double lo = axis < 3 ? cb.lo[axis] : alo, ext = axis < 3 ? cb.hi[axis] - cb.lo[axis] : ahi - alo;
+        if (!(ext > (axis < 3 ? 0.0 : 2.0)) || !std::isfinite(ext)) continue;
         Box bin_box[kBins];
         uint32_t bin_cnt[kBins] = {0};
         for (auto &b : bin_box) b.reset();
         const double scale = kBins / ext;
         for (uint32_t i = begin; i < end; i++) {
           const uint32_t id = out_.perm[i];
-          int b = (int)((cent_[3 * id + axis] - lo) * scale);
+          int b = (int)((key(id, axis) - lo) * scale);
           b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
           bin_cnt[b]++;
           bin_box[b].add(boxes_[id]);
@@ -207,9 +215,9 @@ private:
       std::stable_sort(out_.perm.begin() + begin, out_.perm.begin() + end, [&](uint32_t a, uint32_t b) { return cent_[3 * a + sweep_axis] < cent_[3 * b + sweep_axis]; });
       mid = begin + sweep_left;
     } else if (best_axis >= 0) {
-      const double lo = cb.lo[best_axis], scale = kBins / (cb.hi[best_axis] - cb.lo[best_axis]);
+      const double lo = best_axis < 3 ? cb.lo[best_axis] : alo, scale = kBins / (best_axis < 3 ? cb.hi[best_axis] - cb.lo[best_axis] : ahi - alo);
       auto it = std::partition(out_.perm.begin() + begin, out_.perm.begin() + end, [&](uint32_t id) {
-        int b = (int)((cent_[3 * id + best_axis] - lo) * scale);
+        int b = (int)((key(id, best_axis) - lo) * scale);
         b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
         return b <= best_plane;
       });
