@@ -170,6 +170,9 @@ template <class T> int upload(b200rt_ctx *c, const T *src, size_t count, const T
     if (rc_ != B200RT_OK) return rc_;                                                                                  \
   } while (0)
 
+#ifndef B200_AGGLOMERATIVE_MAX_PRIMS
+#define B200_AGGLOMERATIVE_MAX_PRIMS 256 /* scenes up to this size also get the exact agglomerative tree (O(n^3) on the host) */
+#endif
 #ifndef B200_WIDE_FROM_PRIMS
 #define B200_WIDE_FROM_PRIMS 2048 /* scenes above this many primitives are traversed as a BVH4 (their BVH2 does not fit L1) */
 #endif
@@ -572,7 +575,17 @@ int b200rt_upload_scene(b200rt_ctx *c, const b200rt_scene_desc *d) {
       // experiments: B200RT_SAH_PEEL=0 switches the largest-primitive candidate off, B200RT_SAH_SWEEP=1 the exact sweep on small nodes on,
       // B200RT_SAH_AREA=1 the box-area axis
       auto env_is = [](const char *name, int dflt) { const char *v = std::getenv(name); return (v ? std::atoi(v) : dflt) != 0; };
-      if (!built) bvh = BvhBuilder(fs.boxes, max_leaf, env_is("B200RT_SAH_PEEL", 1), env_is("B200RT_SAH_SWEEP", 0), env_is("B200RT_SAH_AREA", 0)).run();
+      if (!built) {
+        bvh = BvhBuilder(fs.boxes, max_leaf, env_is("B200RT_SAH_PEEL", 1), env_is("B200RT_SAH_SWEEP", 0), env_is("B200RT_SAH_AREA", 0)).run();
+        // a few large overlapping primitives (a room and what stands in it): bottom-up merging often finds the cheaper tree
+        if (fs.boxes.size() >= 3 && fs.boxes.size() <= B200_AGGLOMERATIVE_MAX_PRIMS && env_is("B200RT_AGGLOMERATIVE", 1)) {
+          BuiltBvh alt = build_agglomerative(fs.boxes, max_leaf);
+          if (alt.max_depth <= B200_STACK && alt.sah_cost < 0.99 * bvh.sah_cost) {
+            alt.build_ms += bvh.build_ms;
+            bvh = std::move(alt);
+          }
+        }
+      }
       ordered.resize(fs.entries.size());
       for (size_t k = 0; k < ordered.size(); k++) ordered[k] = fs.entries[bvh.perm[k]];
       // node_step pushes at most one reference per level: a tree deeper than the traversal stack would drop subtrees silently

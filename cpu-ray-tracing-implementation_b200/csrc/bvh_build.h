@@ -359,6 +359,61 @@ inline BuiltBvh finish_tree(const std::vector<BvhNode> &in, uint32_t n_prims, in
   return out;
 }
 
+// Small scenes only (O(n^3)): exact greedy agglomerative clustering (Walter et al. 2008): the pair of clusters whose union box has the
+// smallest area merges, until one cluster is left; then finish_tree.  On a handful of large, overlapping primitives (a room with
+// furniture) top-down centroid splits cannot separate "the walls" from "what stands inside"; bottom-up merging does.  The caller keeps
+// whichever of this tree and the SAH builder's has the lower SAH cost.
+inline BuiltBvh build_agglomerative(const std::vector<Box> &boxes, int max_leaf) {
+  auto t0 = std::chrono::steady_clock::now();
+  struct Cl {
+    float v[6];
+    int32_t ref;
+  };
+  const size_t n = boxes.size();
+  std::vector<Cl> cl(n);
+  double bound[3] = {0, 0, 0};
+  for (size_t i = 0; i < n; i++) {
+    for (int k = 0; k < 3; k++) {
+      float lo = (float)boxes[i].lo[k], hi = (float)boxes[i].hi[k];
+      if ((double)lo > boxes[i].lo[k]) lo = std::nextafterf(lo, -INFINITY);
+      if ((double)hi < boxes[i].hi[k]) hi = std::nextafterf(hi, INFINITY);
+      cl[i].v[2 * k] = lo, cl[i].v[2 * k + 1] = hi;
+      for (float f : {lo, hi})
+        if (std::isfinite(f) && std::fabs((double)f) > bound[k]) bound[k] = std::fabs((double)f);
+    }
+    cl[i].ref = ~(int32_t)((uint32_t)i << 3);
+  }
+  auto union_area = [](const Cl &a, const Cl &b) {
+    double d[3];
+    for (int k = 0; k < 3; k++) d[k] = (double)std::max(a.v[2 * k + 1], b.v[2 * k + 1]) - (double)std::min(a.v[2 * k], b.v[2 * k]);
+    if (!(d[0] >= 0 && d[1] >= 0 && d[2] >= 0)) return 0.0;
+    const double ar = 2 * (d[0] * d[1] + d[1] * d[2] + d[2] * d[0]);
+    return std::isfinite(ar) ? ar : 1e300;
+  };
+  std::vector<BvhNode> topo;
+  topo.reserve(n);
+  while (cl.size() > 1) {
+    size_t bi = 0, bj = 1;
+    double best = INFINITY;
+    for (size_t i = 0; i < cl.size(); i++)
+      for (size_t j = i + 1; j < cl.size(); j++) {
+        const double ar = union_area(cl[i], cl[j]);
+        if (ar < best) best = ar, bi = i, bj = j;
+      }
+    BvhNode nd;
+    std::memset(&nd, 0, sizeof nd);
+    for (int k = 0; k < 6; k++) nd.lbox[k] = cl[bi].v[k], nd.rbox[k] = cl[bj].v[k];
+    nd.left = cl[bi].ref, nd.right = cl[bj].ref;
+    for (int k = 0; k < 3; k++) cl[bi].v[2 * k] = std::min(cl[bi].v[2 * k], cl[bj].v[2 * k]), cl[bi].v[2 * k + 1] = std::max(cl[bi].v[2 * k + 1], cl[bj].v[2 * k + 1]);
+    cl[bi].ref = (int32_t)topo.size();
+    topo.push_back(nd);
+    cl.erase(cl.begin() + (long)bj);
+  }
+  BuiltBvh out = finish_tree(topo, (uint32_t)n, max_leaf, bound);
+  out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  return out;
+}
+
 // BVH2 -> BVH4: every kept node adopts its grandchildren, largest box first, until it has four children or only leaves.
 // Child references keep their encoding (inner: index into the NEW array; leaf: unchanged).
 inline std::vector<BvhNode4> collapse4(const BuiltBvh &b2, int32_t &root4, uint32_t &max_depth4) {

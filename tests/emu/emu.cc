@@ -30,6 +30,8 @@ void *emu_scene_create(const b200rt_scene_desc *d, int leaf_size) {
     e->fs = std::move(fl.out);
     if (leaf_size >= 0) {
       e->bvh = BvhBuilder(e->fs.boxes, leaf_size).run();
+    } else if (leaf_size <= -10) { // the library's small-scene alternative (bvh_build.h: build_agglomerative), -leaf_size - 10 per leaf
+      e->bvh = build_agglomerative(e->fs.boxes, -leaf_size - 10);
     } else {
       // the device PLOC build (csrc/bvh_ploc.cuh) restated serially: clusters in flattener order (the device sorts by Morton code
       // first; any order gives a valid tree), rounds of mutual nearest neighbours within +-radius, children before parents, the

@@ -29,6 +29,27 @@ def test_emu_hits_vs_reference_golden(emu_lib, name, leaf):
         assert ok.all(), f"{name}: {k} differs on {(~ok).sum()} of {keep.sum()} rays"
 
 
+@pytest.mark.parametrize("leaf", [1, 2])
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_emu_agglomerative_tree(emu_lib, name, leaf):
+    """bvh_build.h: build_agglomerative (what b200rt_upload_scene also builds for scenes of up to 256 primitives and keeps when its
+    SAH cost is lower): yet another tree, the same records as the reference."""
+    g = golden(name)
+    if len(g.scene.nodes) > 4000:
+        pytest.skip("O(n^3) builder: small scenes only")
+    es = emu_lib.EmuScene(g.scene, leaf_size=-10 - leaf)
+    info = es.info()
+    assert info["bvh_nodes"] == max(0, info["leaves"] - 1) and 1 <= info["bvh_depth"] <= 64
+    out = es.trace(g["trace_rays"], seed=99)
+    keep = np.ones(len(out["prim"]), bool)
+    if name in VOLUME_SCENES:
+        vol = np.array(sorted(g.volume_prims()))
+        keep = ~np.isin(out["prim"], vol) & ~np.isin(g["trace_prim"], vol)
+    for k in ("prim", "front", "t", "p", "normal", "uv"):
+        ok = same(out[k][keep], g["trace_" + k][keep])
+        assert ok.all(), f"{name}: {k} differs on {(~ok).sum()} of {keep.sum()} rays"
+
+
 @pytest.mark.parametrize("leaf", [1, 2, 3])
 @pytest.mark.parametrize("name", ALL_SCENES)
 def test_emu_clustered_tree_through_finish_tree(emu_lib, name, leaf):
