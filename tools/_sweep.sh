@@ -1,7 +1,6 @@
-# scratch: exact agglomerative tree for small scenes
+# scratch: RTNW (final tree): lane refill threshold, with and without the warp-uniform loop
 mkdir -p gpurun_out
-for rep in 1 2; do for p in 0 1; do
-  B200RT_AGGLOMERATIVE=$p python tools/bench_scenes.py --scenes cornell --reps 3 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"agglomerative=$p\"]/" >> gpurun_out/r02ax_agglomerative_small_scenes.jsonl
-done; done
-grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*\|"build_ms": [0-9.]*\|"sah_cost": [0-9.]*' gpurun_out/r02ax_agglomerative_small_scenes.jsonl | paste - - - - -
-python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "hits_vs_reference or render_matches or edge" 2>&1 | tail -3
+for o in "" "--opt 5=8" "--opt 5=12" "--opt 5=16" "--opt 5=20" "--opt 5=24" "--opt 17=1 --opt 18=24 --opt 5=16" "--opt 17=1 --opt 18=28 --opt 5=16" "--opt 17=1 --opt 18=16 --opt 5=16" "--opt 17=1 --opt 18=24 --opt 5=24"; do
+  python tools/bench_scenes.py --scenes rtnw --reps 2 $o 2>&1 >> gpurun_out/r02ay_rtnw_refill.jsonl
+done
+grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*' gpurun_out/r02ay_rtnw_refill.jsonl | paste - - -

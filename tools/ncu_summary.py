@@ -63,9 +63,11 @@ def kernel(path, index=0):
     src = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     # the source page concatenates the captured launches; take the index-th block
     blocks = src.split('"Kernel Name"')
-    if len(blocks) <= index + 1:
+    n_launches = max(1, len(rows) - 2)
+    views = max(1, (len(blocks) - 1) // n_launches)  # ncu prints every launch once per source view (e.g. SASS, and source + SASS)
+    if len(blocks) <= index * views + 1:
         return
-    rows = list(csv.reader(io.StringIO('"Kernel Name"' + blocks[index + 1])))
+    rows = list(csv.reader(io.StringIO('"Kernel Name"' + blocks[index * views + 1])))
     hdr = rows[1]
     ix = {h: i for i, h in enumerate(hdr)}
     agg = collections.defaultdict(lambda: [0, 0])
