@@ -25,8 +25,21 @@ HD DevCamera make_camera(const b200rt_camera &c) {
 
 // y = row (i), x = column (j).  Draw use: P_CAMERA {u0,u1 = sample_square (:293), u2 = ray time};
 // P_LENS aux=it {u0,u1} = the it-th rejection round of random_in_unit_disk (src/utility.h:46-52).
+// FAST_DEAD (the render path): a fisheye pixel whose whole sample square lies outside the image circle returns its NaN ray without
+// drawing (its time, which only b200rt_generate_rays reports, is then 0 instead of the draw).
+template <bool FAST_DEAD = false>
 DEV Ray generate_ray(const DevCamera &k, const Stream &st, int y, int x) {
   const b200rt_camera &c = k.c;
+  if (FAST_DEAD && c.mode == B200RT_CAM_FISHEYE) {
+    const V dir0 = v3(c.dir[0], c.dir[1], c.dir[2]);
+    const V rd0 = k.d00 + x * k.delta_u + y * k.delta_v;
+    // |offset| <= 0.5 (|delta_u| + |delta_v|) for any sample of the pixel, so rr >= |rd0 - dir| - that; 1e-6 covers every rounding
+    const double least = length(rd0 - dir0) - 0.5 * (length(k.delta_u) + length(k.delta_v));
+    if (least > c.focal_length * (1.0 + 1e-6)) {
+      const double qnan = asin(2.0);
+      return Ray{v3(c.pos[0], c.pos[1], c.pos[2]), v3(qnan, qnan, qnan), 0.0};
+    }
+  }
   const Draws dr = st.get(0, P_CAMERA, 0);
   const double ox = dr.u0 - 0.5, oy = dr.u1 - 0.5;
   const V pos = v3(c.pos[0], c.pos[1], c.pos[2]), dir = v3(c.dir[0], c.dir[1], c.dir[2]);
@@ -40,7 +53,14 @@ DEV Ray generate_ray(const DevCamera &k, const Stream &st, int y, int x) {
     const V rd = k.d00 + x * k.delta_u + y * k.delta_v;
     const V rrd = rd + ox * k.delta_u + oy * k.delta_v;
     const double rr = length(rrd - dir);
-    const double theta = asin(rr / c.focal_length);
+    const double sin_arg = rr / c.focal_length;
+    // outside the image circle asin() is NaN and every later product with it too: the reference's ray is NaN in all three direction
+    // components.  Return that ray before the asin / sin / cos / sqrt chain: 56 % of the Fox config's samples
+    if (!(sin_arg <= 1.0)) {
+      const double qnan = asin(2.0);
+      return Ray{pos, v3(qnan, qnan, qnan), dr.u2};
+    }
+    const double theta = asin(sin_arg);
     const V v1 = unit_vector(dir), v2 = unit_vector(rrd);
     const double sn = sin(theta);
     const double b_prime = sqrt(sn * sn / (1 - dot(v1, v2) * dot(v1, v2)));

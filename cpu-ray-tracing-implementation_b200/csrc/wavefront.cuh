@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(256) k_generate(WaveCtl *c, PathBuf cur, DevCa
       const unsigned long long g = g0 + idx;
       pixel = (uint32_t)(g % wp.npix);
       sample = (uint32_t)wp.spp_begin + (uint32_t)(g / wp.npix);
-      r = generate_ray(cam, Stream{wp.seed, pixel, sample}, (int)(pixel / wp.width), (int)(pixel % wp.width));
+      r = generate_ray<true>(cam, Stream{wp.seed, pixel, sample}, (int)(pixel / wp.width), (int)(pixel % wp.width));
       bad = isnan(r.d.x) || isnan(r.d.y) || isnan(r.d.z); // fisheye outside the image circle: contributes exactly 0
     }
     if (COMPACT) {

@@ -1,6 +1,5 @@
-# scratch: RTNW (final tree): lane refill threshold, with and without the warp-uniform loop
+# scratch: fisheye early-out, second step (no draw for pixels wholly outside the circle)
 mkdir -p gpurun_out
-for o in "" "--opt 5=8" "--opt 5=12" "--opt 5=16" "--opt 5=20" "--opt 5=24" "--opt 17=1 --opt 18=24 --opt 5=16" "--opt 17=1 --opt 18=28 --opt 5=16" "--opt 17=1 --opt 18=16 --opt 5=16" "--opt 17=1 --opt 18=24 --opt 5=24"; do
-  python tools/bench_scenes.py --scenes rtnw --reps 2 $o 2>&1 >> gpurun_out/r02ay_rtnw_refill.jsonl
-done
-grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*' gpurun_out/r02ay_rtnw_refill.jsonl | paste - - -
+python tools/bench_scenes.py --scenes fox,rtow --reps 3 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"fisheye early-out + no draw for dead pixels\"]/" >> gpurun_out/r02ba_fisheye_early_out.jsonl
+grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*\|"msamples_per_s": [0-9.]*' gpurun_out/r02ba_fisheye_early_out.jsonl | paste - - - -
+python -m pytest tests -x -q -m gpu -k "camera or fisheye or fox or converged or render_matches" 2>&1 | tail -3
