@@ -1,5 +1,7 @@
-# scratch: fisheye early-out, second step (no draw for pixels wholly outside the circle)
+# scratch: last build of the round
 mkdir -p gpurun_out
-python tools/bench_scenes.py --scenes fox,rtow --reps 3 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"fisheye early-out + no draw for dead pixels\"]/" >> gpurun_out/r02ba_fisheye_early_out.jsonl
-grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*\|"msamples_per_s": [0-9.]*' gpurun_out/r02ba_fisheye_early_out.jsonl | paste - - - -
-python -m pytest tests -x -q -m gpu -k "camera or fisheye or fox or converged or render_matches" 2>&1 | tail -3
+python -m pytest tests -x -q -m gpu > gpurun_out/r02bb_pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02bb_pytest.log
+python bench.py --impl reference > gpurun_out/r02bb_bench_ref.json 2> gpurun_out/r02bb_bench_ref.err
+python bench.py > gpurun_out/r02bb_bench.json 2> gpurun_out/r02bb_bench.err
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02bb_smoke.log 2>&1
+tail -n 3 gpurun_out/r02bb_pytest.log; head -c 300 gpurun_out/r02bb_bench.json; cat gpurun_out/r02bb_smoke.log
