@@ -32,7 +32,7 @@ def test_emu_hits_vs_reference_golden(emu_lib, name, leaf):
 @pytest.mark.parametrize("leaf", [1, 2])
 @pytest.mark.parametrize("name", ALL_SCENES)
 def test_emu_agglomerative_tree(emu_lib, name, leaf):
-    """bvh_build.h: build_agglomerative (what b200rt_upload_scene also builds for scenes of up to 256 primitives and keeps when its
+    """bvh_build.h: build_agglomerative (what b200rt_upload_scene also builds for scenes of up to 64 primitives and keeps when its
     SAH cost is lower): yet another tree, the same records as the reference."""
     g = golden(name)
     if len(g.scene.nodes) > 4000:
