@@ -127,7 +127,7 @@ DEV void leaf_test(const DevScene &S, int32_t ref, const Ray &r, double lo, doub
 #define B200_PUSH_PREFETCH 0
 #endif
 DEV void prefetch_ref(const DevScene &S, int32_t ref, bool wide) {
-#if B200_PUSH_PREFETCH && !defined(B200_HOST_EMU)
+#if B200_PUSH_PREFETCH == 1 && !defined(B200_HOST_EMU)
   const void *p = ref >= 0 ? (wide ? (const void *)(S.bvh4 + ref) : (const void *)(S.bvh + ref)) : (const void *)(S.entries + ((uint32_t)~ref >> 3));
   asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 #endif
@@ -181,9 +181,21 @@ DEV int32_t node_step4(const DevScene &S, int32_t cur, const RaySetup &rs, float
   cswap4(k1, c1, k3, c3);
   cswap4(k1, c1, k2, c2);
   // cannot overflow: the BVH4 is only used when 3 * depth <= B200_STACK (api.cu: up to three pushes per level)
+#if B200_PUSH_PREFETCH == 2 // only the child that pops next (the second nearest): r02 experiment on the latency-bound Sponza stand-in
+  if (k3 < INF32) stack[sp++] = c3;
+  if (k2 < INF32) stack[sp++] = c2;
+  if (k1 < INF32) {
+    stack[sp++] = c1;
+#ifndef B200_HOST_EMU
+    const void *p = c1 >= 0 ? (const void *)(S.bvh4 + c1) : (const void *)(S.entries + ((uint32_t)~c1 >> 3));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
+  }
+#else
   if (k3 < INF32) stack[sp++] = c3, prefetch_ref(S, c3, true);
   if (k2 < INF32) stack[sp++] = c2, prefetch_ref(S, c2, true);
   if (k1 < INF32) stack[sp++] = c1, prefetch_ref(S, c1, true);
+#endif
   return k0 < INF32 ? c0 : B200_DONE;
 }
 
