@@ -1,7 +1,8 @@
-# scratch: prefetch of the child that pops next (BVH4)
+# scratch: ncu --set full of the shade kernels of wave 0 (RTOW): launch order per wave is miss, lambertian, metal, dielectric
 mkdir -p gpurun_out
-L=$PWD/cpu-ray-tracing-implementation_b200
-for rep in 1 2; do for v in "" _pf2; do
-  B200RT_LIB=$L/libb200rt$v.so python tools/bench_scenes.py --scenes sponza,rtnw --reps 2 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"build$v\"]/" >> gpurun_out/r02bd_prefetch_next_pop.jsonl
-done; done
-grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*' gpurun_out/r02bd_prefetch_next_pop.jsonl | paste - - -
+for k in "1:lambertian" "2:metal" "3:dielectric"; do
+  skip=${k%%:*}; name=${k##*:}
+  ncu --set full --clock-control none --import-source on -k regex:k_shade -s $skip -c 1 -f -o /tmp/r02bf_shade_$name python tools/profile_run.py --scene rtow --spp 20 > gpurun_out/r02bf_ncu_shade_$name.log 2>&1
+  python tools/ncu_summary.py kernel /tmp/r02bf_shade_$name.ncu-rep 0 > gpurun_out/r02bf_shade_${name}_wave0_ncu_full.txt 2>&1
+done
+head -12 gpurun_out/r02bf_shade_lambertian_wave0_ncu_full.txt
