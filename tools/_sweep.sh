@@ -1,8 +1,5 @@
-# scratch: ncu --set full of the shade kernels of wave 0 (RTOW): launch order per wave is miss, lambertian, metal, dielectric
+# scratch: multiply-shift instead of the 64-bit division in k_generate
 mkdir -p gpurun_out
-for k in "1:lambertian" "2:metal" "3:dielectric"; do
-  skip=${k%%:*}; name=${k##*:}
-  ncu --set full --clock-control none --import-source on -k regex:k_shade -s $skip -c 1 -f -o /tmp/r02bf_shade_$name python tools/profile_run.py --scene rtow --spp 20 > gpurun_out/r02bf_ncu_shade_$name.log 2>&1
-  python tools/ncu_summary.py kernel /tmp/r02bf_shade_$name.ncu-rep 0 > gpurun_out/r02bf_shade_${name}_wave0_ncu_full.txt 2>&1
-done
-head -12 gpurun_out/r02bf_shade_lambertian_wave0_ncu_full.txt
+python tools/bench_scenes.py --scenes fox,rtow,cornell,sponza --reps 3 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"fastdiv\"]/" >> gpurun_out/r02bh_generate_fastdiv.jsonl
+grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*\|"msamples_per_s": [0-9.]*' gpurun_out/r02bh_generate_fastdiv.jsonl | paste - - - -
+python -m pytest tests -x -q -m gpu -k "render or sample_ranges or fisheye or wave or pipelines or converged or group" 2>&1 | tail -3
