@@ -1,5 +1,6 @@
-# scratch: multiply-shift instead of the 64-bit division in k_generate
+# scratch: last build of the round
 mkdir -p gpurun_out
-python tools/bench_scenes.py --scenes fox,rtow,cornell,sponza --reps 3 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"fastdiv\"]/" >> gpurun_out/r02bh_generate_fastdiv.jsonl
-grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*\|"msamples_per_s": [0-9.]*' gpurun_out/r02bh_generate_fastdiv.jsonl | paste - - - -
-python -m pytest tests -x -q -m gpu -k "render or sample_ranges or fisheye or wave or pipelines or converged or group" 2>&1 | tail -3
+python -m pytest tests -x -q -m gpu > gpurun_out/r02bi_pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02bi_pytest.log
+python bench.py > gpurun_out/r02bi_bench.json 2> gpurun_out/r02bi_bench.err
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02bi_smoke.log 2>&1
+tail -n 3 gpurun_out/r02bi_pytest.log; head -c 300 gpurun_out/r02bi_bench.json; cat gpurun_out/r02bi_smoke.log
