@@ -1,6 +1,7 @@
-# scratch: last build of the round
+# scratch: shared-reciprocal exact vec3 division (round-1 experiment) again, now under the two-pipeline schedule
 mkdir -p gpurun_out
-python -m pytest tests -x -q -m gpu > gpurun_out/r02bi_pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02bi_pytest.log
-python bench.py > gpurun_out/r02bi_bench.json 2> gpurun_out/r02bi_bench.err
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02bi_smoke.log 2>&1
-tail -n 3 gpurun_out/r02bi_pytest.log; head -c 300 gpurun_out/r02bi_bench.json; cat gpurun_out/r02bi_smoke.log
+L=$PWD/cpu-ray-tracing-implementation_b200
+for rep in 1 2; do for v in "" _rcp; do
+  B200RT_LIB=$L/libb200rt$v.so python tools/bench_scenes.py --scenes rtow,cornell,rtnw,fox,sponza --reps 2 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"build$v\"]/" >> gpurun_out/r02bj_shared_rcp_div.jsonl
+done; done
+grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*' gpurun_out/r02bj_shared_rcp_div.jsonl | paste - - -
