@@ -1166,6 +1166,7 @@ int b200rt_render_device(b200rt_ctx *c, uint64_t seed, int spp_begin, int spp_en
   if (mirror && (rc = prepare_mirror(c)) != B200RT_OK) return rc;
 
   WaveParams wp[B200_MAX_PIPELINES];
+  std::memset(wp, 0, sizeof wp); // padding bytes too: the structure is part of the wave graph's cache key
   unsigned long long tot[B200_MAX_PIPELINES] = {0};
   uint32_t cap[B200_MAX_PIPELINES] = {0};
   for (int p = 0; p < n_pipe; p++) {
