@@ -1,7 +1,7 @@
-# scratch: BVH width on the small scenes with the round-2 kernels
+# scratch: solid-colour background added by the extend kernel itself (fused_miss = 2)
 mkdir -p gpurun_out
-for o in "" "--opt 12=4" "--opt 12=4 --opt 17=0" "--opt 3=2"; do
-  python tools/bench_scenes.py --scenes rtow,cornell,fox --reps 2 $o 2>&1 >> gpurun_out/r02bk_small_scene_width.jsonl
-done
-python tools/bench_scenes.py --scenes rtnw,sponza --reps 2 --opt 12=2 2>&1 >> gpurun_out/r02bk_small_scene_width.jsonl
-grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*' gpurun_out/r02bk_small_scene_width.jsonl | paste - - -
+for rep in 1 2; do for p in 0 1; do
+  B200RT_FUSE_SOLID_BG=$p python tools/bench_scenes.py --scenes rtow,cornell,rtnw,fox,sponza --reps 2 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"fuse_solid_bg=$p\"]/" >> gpurun_out/r02bl_fused_solid_background.jsonl
+done; done
+grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*\|"kernel_launches": [0-9]*' gpurun_out/r02bl_fused_solid_background.jsonl | paste - - - -
+python -m pytest tests -x -q -m gpu 2>&1 | tail -2
