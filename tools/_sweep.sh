@@ -1,7 +1,6 @@
-# scratch: one-colour background finished by k_classify (no miss queue, no miss launch)
+# scratch: the head of the branch, built from scratch by __graft_entry__.build(), on a B200
 mkdir -p gpurun_out
-for rep in 1 2; do for p in 0 1; do
-  B200RT_CLASSIFY_BG=$p python tools/bench_scenes.py --scenes rtow,cornell,rtnw --reps 2 2>&1 | sed "s/\"opts\": \[\]/\"opts\": [\"classify_bg=$p\"]/" >> gpurun_out/r02bm_classify_solid_background.jsonl
-done; done
-grep -o '"scene": "[a-z]*"\|"opts": [^]]*]\|"mrays_per_s": [0-9.]*\|"kernel_launches": [0-9]*' gpurun_out/r02bm_classify_solid_background.jsonl | paste - - - -
-python -m pytest tests -x -q -m gpu 2>&1 | tail -2
+python -m pytest tests -x -q -m gpu > gpurun_out/r02bn_pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02bn_pytest.log
+python bench.py > gpurun_out/r02bn_bench.json 2> gpurun_out/r02bn_bench.err
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02bn_smoke.log 2>&1
+tail -n 3 gpurun_out/r02bn_pytest.log; head -c 300 gpurun_out/r02bn_bench.json; cat gpurun_out/r02bn_smoke.log
