@@ -474,6 +474,10 @@ def test_device_built_bvh_sponza_standin():
             assert same(host[k], ploc[k]).all(), k
         assert pinfo["n_prims"] == hinfo["n_prims"] and pinfo["build_ms"] < hinfo["build_ms"]
         assert pinfo["n_leaves"] < pinfo["n_prims"]  # leaf pairs were formed
+        c.upload_scene(sc)  # node indices come from a scan, not from atomics: the same scene gives the same tree
+        again = c.bvh_info()
+        for k in ("n_nodes", "n_leaves", "max_depth", "sah_cost"):
+            assert again[k] == pinfo[k], k
         print(f"                     device PLOC + host finish {pinfo['build_ms']:.2f} ms (cost {pinfo['sah_cost']:.1f}, depth {pinfo['max_depth']}, {pinfo['n_nodes']} BVH4 nodes vs {hinfo['n_nodes']})")
     finally:
         c.close()
