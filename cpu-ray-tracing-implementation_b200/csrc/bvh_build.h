@@ -10,6 +10,7 @@
 #include <cmath>
 #include <numeric>
 #include <stdexcept>
+#include <thread>
 
 #include "flatten.h"
 
@@ -26,8 +27,12 @@ struct BuiltBvh {
 
 class BvhBuilder {
 public:
-  BvhBuilder(const std::vector<Box> &boxes, int max_leaf, bool peel = true, bool sweep = false, bool area_axis = false)
-      : boxes_(boxes), max_leaf_(std::max(1, std::min(8, max_leaf))), peel_(peel), sweep_(sweep), area_axis_(area_axis) {}
+  // threads: 0 = as many as the machine has (large scenes only: subtrees of >= kParallelMin primitives in the top kParallelDepth
+  // levels are built by their own threads), 1 = serial.  The tree does not depend on it: node indices, boxes and the entry
+  // permutation are identical (tests/test_emu_device_functions.py), only the SAH cost's last bits (summation order) may differ.
+  BvhBuilder(const std::vector<Box> &boxes, int max_leaf, bool peel = true, bool sweep = false, bool area_axis = false, int threads = 0)
+      : boxes_(boxes), max_leaf_(std::max(1, std::min(8, max_leaf))), peel_(peel), sweep_(sweep), area_axis_(area_axis),
+        parallel_(threads == 0 ? std::thread::hardware_concurrency() > 1 : threads > 1) {}
 
   BuiltBvh run() {
     auto t0 = std::chrono::steady_clock::now();
@@ -48,9 +53,13 @@ public:
     }
     if (n > 0) {
       Box rb;
-      out_.root = build(0, (uint32_t)n, 1, rb);
+      Acc acc;
+      out_.root = build(acc, 0, (uint32_t)n, 1, rb);
+      out_.nodes = std::move(acc.nodes);
+      out_.n_leaves = acc.n_leaves, out_.max_depth = acc.max_depth;
+      for (int k = 0; k < 3; k++) out_.bound[k] = acc.bound[k];
       root_area_ = rb.area();
-      if (root_area_ > 0) out_.sah_cost = cost_acc_ / root_area_;
+      if (root_area_ > 0) out_.sah_cost = acc.cost / root_area_;
     }
     out_.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return std::move(out_);
@@ -64,8 +73,16 @@ private:
   bool peel_, sweep_, area_axis_;
   std::vector<double> cent_, area_, larea_;
   double key(uint32_t id, int axis) const { return axis < 3 ? cent_[3 * id + axis] : larea_[id]; } // axis 3: log2 of the box area
+  bool parallel_;
+  static constexpr uint32_t kParallelMin = 16384, kParallelDepth = 5;
   BuiltBvh out_;
-  double cost_acc_ = 0, root_area_ = 0;
+  double root_area_ = 0;
+  struct Acc { // what one (sub)tree build produces besides its share of out_.perm
+    std::vector<BvhNode> nodes; // indices local to this vector
+    double cost = 0;
+    uint32_t n_leaves = 0, max_depth = 0;
+    double bound[3] = {0, 0, 0};
+  };
 
   static float round_down(double x) {
     float f = (float)x;
@@ -77,25 +94,25 @@ private:
     if ((double)f < x) f = std::nextafterf(f, INFINITY);
     return f;
   }
-  void set_box(float dst[6], const Box &b) {
+  static void set_box(Acc &acc, float dst[6], const Box &b) {
     for (int k = 0; k < 3; k++) {
       dst[2 * k] = round_down(b.lo[k]);
       dst[2 * k + 1] = round_up(b.hi[k]);
       for (int e = 0; e < 2; e++) {
         const double a = std::fabs((double)dst[2 * k + e]);
-        if (std::isfinite(a) && a > out_.bound[k]) out_.bound[k] = a;
+        if (std::isfinite(a) && a > acc.bound[k]) acc.bound[k] = a;
       }
     }
   }
 
-  int32_t make_leaf(uint32_t begin, uint32_t end, uint32_t depth, const Box &b) {
-    out_.n_leaves++;
-    out_.max_depth = std::max(out_.max_depth, depth);
-    cost_acc_ += b.area() * (end - begin);
+  static int32_t make_leaf(Acc &acc, uint32_t begin, uint32_t end, uint32_t depth, const Box &b) {
+    acc.n_leaves++;
+    acc.max_depth = std::max(acc.max_depth, depth);
+    acc.cost += b.area() * (end - begin);
     return ~(int32_t)((begin << 3) | (end - begin - 1));
   }
 
-  int32_t build(uint32_t begin, uint32_t end, uint32_t depth, Box &bounds) {
+  int32_t build(Acc &acc, uint32_t begin, uint32_t end, uint32_t depth, Box &bounds) {
     const uint32_t count = end - begin;
     bounds.reset();
     Box cb;
@@ -109,7 +126,7 @@ private:
       if (area_[id] > big_area) big_area = area_[id], big = i;
       alo = std::min(alo, larea_[id]), ahi = std::max(ahi, larea_[id]);
     }
-    if (count == 1) return make_leaf(begin, end, depth, bounds);
+    if (count == 1) return make_leaf(acc, begin, end, depth, bounds);
 
     // best binned SAH split
     double best_cost = INFINITY;
@@ -205,7 +222,7 @@ private:
       // leaf cost: count intersections; split cost: one node (two boxes, ~1.2 intersections' worth) + children
       const double leaf_cost = (double)count * parent_area;
       const double split_cost = (best_axis < 0 && peel < 0 && sweep_axis < 0) ? INFINITY : 1.2 * parent_area + best_cost;
-      if (leaf_cost <= split_cost) return make_leaf(begin, end, depth, bounds);
+      if (leaf_cost <= split_cost) return make_leaf(acc, begin, end, depth, bounds);
     }
     uint32_t mid;
     if (peel >= 0) {
@@ -233,19 +250,46 @@ private:
       std::nth_element(out_.perm.begin() + begin, out_.perm.begin() + mid, out_.perm.begin() + end,
                        [&](uint32_t a, uint32_t b) { return cent_[3 * a + axis] < cent_[3 * b + axis]; });
     }
-    const uint32_t me = (uint32_t)out_.nodes.size();
-    out_.nodes.emplace_back();
-    std::memset(&out_.nodes[me], 0, sizeof(BvhNode));
-    cost_acc_ += 1.2 * parent_area;
+    const uint32_t me = (uint32_t)acc.nodes.size();
+    acc.nodes.emplace_back();
+    std::memset(&acc.nodes[me], 0, sizeof(BvhNode));
+    acc.cost += 1.2 * parent_area;
     Box lb, rb;
-    const int32_t l = build(begin, mid, depth + 1, lb);
-    const int32_t r = build(mid, end, depth + 1, rb);
-    BvhNode &nd = out_.nodes[me];
+    int32_t l, r;
+    if (parallel_ && depth <= kParallelDepth && mid - begin >= kParallelMin && end - mid >= kParallelMin) {
+      // the two halves work on disjoint ranges of out_.perm and read everything else: the left one gets its own thread, both
+      // build into their own node vectors, which are then appended in the order the serial recursion would have produced
+      Acc la, ra;
+      std::thread left([&] { l = build(la, begin, mid, depth + 1, lb); });
+      r = build(ra, mid, end, depth + 1, rb);
+      left.join();
+      l = splice(acc, la, l);
+      r = splice(acc, ra, r);
+    } else {
+      l = build(acc, begin, mid, depth + 1, lb);
+      r = build(acc, mid, end, depth + 1, rb);
+    }
+    BvhNode &nd = acc.nodes[me];
     nd.left = l;
     nd.right = r;
-    set_box(nd.lbox, lb);
-    set_box(nd.rbox, rb);
+    set_box(acc, nd.lbox, lb);
+    set_box(acc, nd.rbox, rb);
     return (int32_t)me;
+  }
+
+  // appends a finished subtree to `acc`; returns its root reference in acc's numbering
+  static int32_t splice(Acc &acc, Acc &sub, int32_t root) {
+    const int32_t off = (int32_t)acc.nodes.size();
+    for (BvhNode nd : sub.nodes) {
+      if (nd.left >= 0) nd.left += off;
+      if (nd.right >= 0) nd.right += off;
+      acc.nodes.push_back(nd);
+    }
+    acc.cost += sub.cost;
+    acc.n_leaves += sub.n_leaves;
+    acc.max_depth = std::max(acc.max_depth, sub.max_depth);
+    for (int k = 0; k < 3; k++) acc.bound[k] = std::max(acc.bound[k], sub.bound[k]);
+    return root >= 0 ? root + off : root;
   }
 };
 

@@ -28,7 +28,9 @@ void *emu_scene_create(const b200rt_scene_desc *d, int leaf_size) {
     Flattener fl(*d);
     fl.run();
     e->fs = std::move(fl.out);
-    if (leaf_size >= 0) {
+    if (leaf_size >= 100) { // the host builder on ONE thread (leaf_size - 100 per leaf): the tree the threaded build has to reproduce
+      e->bvh = BvhBuilder(e->fs.boxes, leaf_size - 100, true, false, false, 1).run();
+    } else if (leaf_size >= 0) {
       e->bvh = BvhBuilder(e->fs.boxes, leaf_size).run();
     } else if (leaf_size <= -10) { // the library's small-scene alternative (bvh_build.h: build_agglomerative), -leaf_size - 10 per leaf
       e->bvh = build_agglomerative(e->fs.boxes, -leaf_size - 10);
@@ -119,6 +121,18 @@ void *emu_scene_create(const b200rt_scene_desc *d, int leaf_size) {
   return e;
 }
 void emu_scene_destroy(void *h) { delete static_cast<EmuScene *>(h); }
+uint64_t emu_scene_bvh_hash(void *h) { // FNV-1a over the node array and the entry permutation
+  auto *e = static_cast<EmuScene *>(h);
+  uint64_t x = 1469598103934665603ull;
+  auto eat = [&](const void *p, size_t n) {
+    const unsigned char *b = static_cast<const unsigned char *>(p);
+    for (size_t i = 0; i < n; i++) x = (x ^ b[i]) * 1099511628211ull;
+  };
+  eat(e->bvh.nodes.data(), e->bvh.nodes.size() * sizeof(BvhNode));
+  eat(e->bvh.perm.data(), e->bvh.perm.size() * sizeof(uint32_t));
+  eat(&e->bvh.root, sizeof e->bvh.root);
+  return x;
+}
 void emu_scene_info(void *h, uint32_t *out6) {
   auto *e = static_cast<EmuScene *>(h);
   out6[0] = (uint32_t)e->bvh.nodes.size(), out6[1] = e->bvh.n_leaves, out6[2] = (uint32_t)e->ordered.size(), out6[3] = e->bvh.max_depth;

@@ -56,6 +56,11 @@ class EmuScene:
         if not self.h:
             raise RuntimeError("emu_scene_create failed")
 
+    def bvh_hash(self):
+        f = lib().emu_scene_bvh_hash
+        f.argtypes, f.restype = [C.c_void_p], C.c_uint64
+        return f(self.h)
+
     def info(self):
         a = np.zeros(6, np.uint32)
         lib().emu_scene_info(self.h, a.ctypes.data)

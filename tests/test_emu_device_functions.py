@@ -29,6 +29,18 @@ def test_emu_hits_vs_reference_golden(emu_lib, name, leaf):
         assert ok.all(), f"{name}: {k} differs on {(~ok).sum()} of {keep.sum()} rays"
 
 
+def test_threaded_host_build_gives_the_serial_tree(emu_lib):
+    """bvh_build.h: subtrees of >= 16384 primitives in the top levels are built by their own threads; node numbering, boxes and
+    the entry permutation must be those of the one-thread build (262 268 primitives: the Sponza stand-in)."""
+    import importlib
+
+    pkg = importlib.import_module("cpu-ray-tracing-implementation_b200")
+    sc = pkg.scene.sponza_standin_scene()
+    a, b = emu_lib.EmuScene(sc, leaf_size=2), emu_lib.EmuScene(sc, leaf_size=102)
+    assert a.info() == b.info()
+    assert a.bvh_hash() == b.bvh_hash()
+
+
 @pytest.mark.parametrize("leaf", [1, 2])
 @pytest.mark.parametrize("name", ALL_SCENES)
 def test_emu_agglomerative_tree(emu_lib, name, leaf):
